@@ -1,0 +1,113 @@
+"""ctypes binding of libb200img.so (the C ABI in include/b200img.h).
+
+The library is built in-tree by ``make`` (or ``__graft_entry__.build()``) and loaded from
+``mpi_cuda_imagemanipulation_b200/lib``. There is no pure-Python fallback for the compute path:
+if the shared object is missing the import fails loudly, so a GPU box can never silently run a
+slower stand-in.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_REPO = os.path.dirname(_HERE)
+LIB_PATH = os.path.join(_HERE, "lib", "libb200img.so")
+
+B2I_MAX_OPS = 16
+B2I_MAX_GPUS = 16
+
+# b2i_status
+OK, ERR_ARG, ERR_IO, ERR_CUDA, ERR_UNSUPPORTED, ERR_NO_DEVICE, ERR_TIMEOUT, ERR_NOMEM = (
+    0, -1, -2, -3, -4, -5, -6, -7)
+# b2i_opkind
+OP_GRAY_REF, OP_GRAY_CV, OP_LUT, OP_STENCIL, OP_SOBEL, OP_EXPAND = 1, 2, 3, 4, 5, 6
+# b2i_border
+BORDER_REF, BORDER_REFLECT101, BORDER_REPLICATE, BORDER_ZERO = 0, 1, 2, 3
+BORDERS = {"ref": 0, "reflect101": 1, "reflect": 1, "replicate": 2, "zero": 3, None: -1, "": -1,
+           "default": -1}
+# b2i_order
+ORDER_BGR, ORDER_RGB = 0, 1
+ORDERS = {"bgr": 0, "rgb": 1}
+
+
+class Op(C.Structure):
+    _fields_ = [
+        ("kind", C.c_int32), ("border", C.c_int32), ("ksize", C.c_int32), ("shift", C.c_int32),
+        ("bias", C.c_int32), ("reserved", C.c_int32),
+        ("weights", C.c_int8 * 32), ("lut", C.c_uint8 * 256), ("name", C.c_char * 24),
+    ]
+
+
+class ChainStruct(C.Structure):
+    _fields_ = [("n_ops", C.c_int32), ("order", C.c_int32), ("ops", Op * B2I_MAX_OPS)]
+
+
+class B200ImgError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"b200img error {code}: {msg}")
+        self.code = code
+
+
+def build(verbose: bool = False) -> None:
+    """Runs ``make`` at the repo root (library + CLI, sm_100a)."""
+    res = subprocess.run(["make", "-C", _REPO, "-j8"], capture_output=not verbose, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("building libb200img.so failed:\n" + (res.stdout or "") + (res.stderr or ""))
+
+
+def _load() -> C.CDLL:
+    if not os.path.exists(LIB_PATH):
+        if os.environ.get("B200IMG_NO_AUTOBUILD"):
+            raise ImportError(f"{LIB_PATH} is missing; run `make` at the repo root")
+        build()
+    return C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+
+
+lib = _load()
+lib.b2i_last_error.restype = C.c_char_p
+lib.b2i_version.restype = C.c_char_p
+
+
+def check(rc: int) -> int:
+    if rc < 0:
+        raise B200ImgError(rc, lib.b2i_last_error().decode("utf-8", "replace"))
+    return rc
+
+
+def _sig(name, restype, *argtypes):
+    fn = getattr(lib, name)
+    fn.restype = restype
+    fn.argtypes = list(argtypes)
+    return fn
+
+
+_P = C.POINTER
+u8p = C.c_void_p  # raw addresses: numpy .ctypes.data / torch .data_ptr()
+
+_sig("b2i_chain_parse", C.c_int, C.c_char_p, C.c_int, C.c_int, _P(ChainStruct))
+_sig("b2i_chain_preset", C.c_int, C.c_char_p, C.c_int, _P(ChainStruct))
+_sig("b2i_chain_out_channels", C.c_int, _P(ChainStruct), C.c_int)
+_sig("b2i_chain_halo", C.c_int, _P(ChainStruct))
+_sig("b2i_chain_describe", C.c_int, _P(ChainStruct), C.c_char_p, C.c_size_t)
+_sig("b2i_lut_contrast_ref", None, C.c_float, u8p)
+_sig("b2i_lut_contrast_cv", None, C.c_double, u8p)
+_sig("b2i_band_rows", C.c_int, C.c_int, C.c_int, C.c_int, _P(C.c_int), _P(C.c_int))
+_sig("b2i_host_run", C.c_int, _P(ChainStruct), u8p, C.c_int, C.c_int, C.c_int, C.c_size_t, u8p,
+     C.c_size_t)
+_sig("b2i_host_run_rows", C.c_int, _P(ChainStruct), u8p, C.c_int, C.c_int, C.c_int, C.c_size_t,
+     C.c_int, C.c_int, u8p, C.c_size_t)
+_sig("b2i_host_run_ranks", C.c_int, _P(ChainStruct), u8p, C.c_int, C.c_int, C.c_int, C.c_size_t,
+     u8p, C.c_size_t, C.c_int, C.c_int, _P(C.c_double))
+_sig("b2i_read_pnm", C.c_int, C.c_char_p, C.c_int, _P(C.c_void_p), _P(C.c_int), _P(C.c_int),
+     _P(C.c_int))
+_sig("b2i_write_pnm", C.c_int, C.c_char_p, C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_size_t)
+_sig("b2i_read_raw", C.c_int, C.c_char_p, C.c_int, C.c_int, C.c_int, _P(C.c_void_p))
+_sig("b2i_write_raw", C.c_int, C.c_char_p, u8p, C.c_int, C.c_int, C.c_int, C.c_size_t)
+_sig("b2i_free", None, C.c_void_p)
+_sig("b2i_synth_image", C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_uint32)
+
+
+def has(symbol: str) -> bool:
+    return hasattr(lib, symbol)
