@@ -1,0 +1,255 @@
+// b200img — command-line entry point.
+//
+// The reference's entry points are two main() functions without any options: input path, output
+// name, contrast factor and the 3x3/5x5 switch are literals, and argv only reaches MPI_Init
+// (kernel.cu:96-110,236; kern.cpp:17-33,92). This binary keeps that zero-argument behaviour —
+// run it bare and it performs gray -> contrast 3.5 -> emboss 3x3 -> BGR and writes
+// imageFinalEmboss2.ppm — and turns every literal into a flag. `-np N` is accepted the way
+// `mpirun -np N ./prog` was used: it sets the number of GPUs (cuda backend) or host ranks.
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "b200img.h"
+
+namespace {
+
+struct Options {
+  std::string input, output = "imageFinalEmboss2.ppm", format, filters, preset, border,
+              backend = "auto", order = "bgr", synth;
+  int width = 0, height = 0, channels = 3, gpus = 1, ranks = 0, root = 0, iters = 1;
+  bool json = false, verbose = false, seams = false, topology = false, no_tma = false,
+       naive = false, help = false, resident = false;
+};
+
+void usage() {
+  puts(
+      "b200img " B2I_VERSION " - Blackwell-native distributed image filtering\n"
+      "usage: b200img [options]          (no options: the reference pipeline on 3.ppm or a test card)\n"
+      "  --input F            PPM (P6), PGM (P5) or raw input file\n"
+      "  --output F           output file (default imageFinalEmboss2.ppm)\n"
+      "  --format ppm|pgm|raw file format (default: by extension)\n"
+      "  --width W --height H --channels C   geometry of raw input\n"
+      "  --synth WxH          use a synthetic WxH test card as input\n"
+      "  --order bgr|rgb      channel order in memory (default bgr, like cv::imread)\n"
+      "  --filters SPEC       e.g. gray,contrast:3.5,emboss3  (see include/b200img.h)\n"
+      "  --preset NAME        kernel_cu (default) | kernel_cu_5x5 | kern_cpp\n"
+      "  --border B           ref|reflect101|replicate|zero for stencils without an @border\n"
+      "  --backend B          cuda | host | naive | auto (default: cuda when a GPU is present)\n"
+      "  --gpus N | -np N     GPUs (cuda) or host workers (host) sharing the image by row bands\n"
+      "  --ranks N            host workers for --backend host\n"
+      "  --seams              host backend: filter bands in isolation like the reference\n"
+      "  --root G             GPU that owns input and output (default 0)\n"
+      "  --iters K            timed repetitions\n"
+      "  --no-tma             force the plain ld/st tile loaders\n"
+      "  --topology           print the GPU / NVLink topology as JSON and exit\n"
+      "  --json               one JSON line with timings instead of the reference-style text\n"
+      "  --verbose            per-rank geometry lines like kernel.cu:186-188");
+}
+
+bool ends_with(const std::string& s, const char* suf) {
+  const size_t n = strlen(suf);
+  return s.size() >= n && s.compare(s.size() - n, n, suf) == 0;
+}
+
+int fail(const char* what) {
+  fprintf(stderr, "b200img: %s: %s\n", what, b2i_last_error());
+  return 1;
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+  Options o;
+  for (int i = 1; i < argc; ++i) {
+    const std::string a = argv[i];
+    auto next = [&](const char* name) -> const char* {
+      if (i + 1 >= argc) {
+        fprintf(stderr, "b200img: %s needs a value\n", name);
+        exit(2);
+      }
+      return argv[++i];
+    };
+    if (a == "--input" || a == "-i") o.input = next("--input");
+    else if (a == "--output" || a == "-o") o.output = next("--output");
+    else if (a == "--format") o.format = next("--format");
+    else if (a == "--width") o.width = atoi(next("--width"));
+    else if (a == "--height") o.height = atoi(next("--height"));
+    else if (a == "--channels") o.channels = atoi(next("--channels"));
+    else if (a == "--synth") o.synth = next("--synth");
+    else if (a == "--order") o.order = next("--order");
+    else if (a == "--filters" || a == "-f") o.filters = next("--filters");
+    else if (a == "--preset") o.preset = next("--preset");
+    else if (a == "--border") o.border = next("--border");
+    else if (a == "--backend") o.backend = next("--backend");
+    else if (a == "--gpus" || a == "-np" || a == "-n") o.gpus = atoi(next("--gpus"));
+    else if (a == "--ranks") o.ranks = atoi(next("--ranks"));
+    else if (a == "--root") o.root = atoi(next("--root"));
+    else if (a == "--iters") o.iters = atoi(next("--iters"));
+    else if (a == "--seams") o.seams = true;
+    else if (a == "--resident") o.resident = true;
+    else if (a == "--no-tma") o.no_tma = true;
+    else if (a == "--topology") o.topology = true;
+    else if (a == "--json") o.json = true;
+    else if (a == "--verbose" || a == "-v") o.verbose = true;
+    else if (a == "--help" || a == "-h") o.help = true;
+    else {
+      fprintf(stderr, "b200img: unknown option '%s' (try --help)\n", a.c_str());
+      return 2;
+    }
+  }
+  if (o.help) {
+    usage();
+    return 0;
+  }
+  if (o.topology) {
+    std::vector<char> buf(1 << 16);
+    if (b2i_topology_json(buf.data(), buf.size()) != B2I_OK) return fail("topology");
+    puts(buf.data());
+    return 0;
+  }
+  const int order = o.order == "rgb" ? B2I_ORDER_RGB : B2I_ORDER_BGR;
+
+  // ---- chain ------------------------------------------------------------------------------
+  b2i_chain_t chain;
+  int border = -1;
+  if (!o.border.empty()) {
+    b2i_chain_t probe;
+    if (b2i_chain_parse(("emboss3@" + o.border).c_str(), -1, order, &probe) != B2I_OK)
+      return fail("--border");
+    border = probe.ops[0].border;
+  }
+  if (!o.filters.empty()) {
+    if (b2i_chain_parse(o.filters.c_str(), border, order, &chain) != B2I_OK) return fail("--filters");
+  } else {
+    if (b2i_chain_preset(o.preset.empty() ? "kernel_cu" : o.preset.c_str(), order, &chain) != B2I_OK)
+      return fail("--preset");
+  }
+
+  // ---- input: rank-0-only load in the reference (kernel.cu:109-119) ------------------------
+  uint8_t* img = nullptr;
+  int W = 0, H = 0, C = 0;
+  std::string source;
+  if (!o.synth.empty()) {
+    if (sscanf(o.synth.c_str(), "%dx%d", &W, &H) != 2 || W <= 0 || H <= 0) {
+      fprintf(stderr, "b200img: --synth wants WxH\n");
+      return 2;
+    }
+    C = o.channels;
+  } else {
+    if (o.input.empty()) {
+      const char* env = getenv("B200IMG_INPUT");
+      if (env && *env) o.input = env;
+      else if (FILE* f = fopen("3.ppm", "rb")) {  // the reference reads ...\\PKA_img\\3.jpg
+        fclose(f);
+        o.input = "3.ppm";
+      }
+    }
+    if (o.input.empty()) {
+      W = 1920;
+      H = 1080;
+      C = 3;
+    }
+  }
+  if (!o.input.empty()) {
+    const bool raw = o.format == "raw" || (o.format.empty() && ends_with(o.input, ".raw"));
+    int rc;
+    if (raw) {
+      W = o.width;
+      H = o.height;
+      C = o.channels;
+      rc = b2i_read_raw(o.input.c_str(), W, H, C, &img);
+    } else {
+      rc = b2i_read_pnm(o.input.c_str(), order, &img, &W, &H, &C);
+    }
+    if (rc != B2I_OK) {
+      // kernel.cu:111-114 prints this and returns 1 while its peers hang in MPI_Barrier; here
+      // nothing has been launched yet, so the failure is clean
+      fprintf(stderr, "!!! Failed imread(): image not found\nb2i: %s\n", b2i_last_error());
+      return 1;
+    }
+    source = o.input;
+  } else {
+    img = (uint8_t*)malloc((size_t)W * H * C);
+    if (!img || b2i_synth_image(img, W, H, C, (size_t)W * C, 1) != B2I_OK) return fail("synth");
+    source = "synthetic test card";
+  }
+  const int out_c = b2i_chain_out_channels(&chain, C);
+  if (out_c < 0) return fail("chain");
+  std::vector<uint8_t> out((size_t)W * H * out_c);
+
+  // ---- run ----------------------------------------------------------------------------------
+  std::string backend = o.backend;
+  if (backend == "auto") backend = b2i_cuda_device_count() > 0 ? "cuda" : "host";
+  const int n = backend == "host" ? (o.ranks > 0 ? o.ranks : o.gpus) : o.gpus;
+  if (o.verbose) {  // kernel.cu:186-188 prints these from every rank
+    for (int r = 0; r < n; ++r) {
+      int y0, y1;
+      b2i_band_rows(H, n, r, &y0, &y1);
+      printf("[rank %d] Image properties: W=%d   H=%d   C=%d   rows [%d,%d)\n", r, W, y1 - y0, C, y0, y1);
+    }
+  }
+  double kernel_ms = 0, total_ms = 0;
+  std::vector<char> report(1 << 14, 0);
+  const auto t0 = std::chrono::steady_clock::now();
+  if (backend == "host") {
+    double best = 1e30;
+    for (int it = 0; it < (o.iters > 0 ? o.iters : 1); ++it) {
+      double ms = 0;
+      if (b2i_host_run_ranks(&chain, img, W, H, C, (size_t)W * C, out.data(), (size_t)W * out_c,
+                             n > 0 ? n : 1, o.seams, &ms) != B2I_OK)
+        return fail("host backend");
+      if (ms < best) best = ms;
+    }
+    kernel_ms = best;
+  } else if (backend == "cuda" || backend == "naive") {
+    const int flags = (o.no_tma ? B2I_LAUNCH_NO_TMA : 0) | (backend == "naive" ? B2I_LAUNCH_NAIVE : 0);
+    int rc;
+    if (n <= 1 && !o.resident)
+      rc = b2i_cuda_run_host_image(&chain, img, W, H, C, (size_t)W * C, out.data(),
+                                   (size_t)W * out_c, o.root, o.iters, flags, &kernel_ms, &total_ms);
+    else
+      rc = b2i_ctx_run_cli(n, o.root, &chain, img, W, H, C, out.data(), o.iters, flags, o.resident,
+                           &kernel_ms, &total_ms, report.data(), report.size());
+    if (rc != B2I_OK) return fail("cuda backend");
+  } else {
+    fprintf(stderr, "b200img: unknown backend '%s'\n", backend.c_str());
+    return 2;
+  }
+  const double wall_ms =
+      std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  if (total_ms == 0) total_ms = wall_ms;
+
+  // ---- output: rank 0 writes the gathered image (kernel.cu:229-237) --------------------------
+  const bool raw_out = o.format == "raw" || ends_with(o.output, ".raw");
+  std::string outp = o.output;
+  if (!raw_out && out_c == 1 && ends_with(outp, ".ppm")) outp.replace(outp.size() - 3, 3, "pgm");
+  const int wrc = raw_out ? b2i_write_raw(outp.c_str(), out.data(), W, H, out_c, (size_t)W * out_c)
+                          : b2i_write_pnm(outp.c_str(), order, out.data(), W, H, out_c, (size_t)W * out_c);
+  if (wrc != B2I_OK) return fail("write");
+
+  char desc[512];
+  b2i_chain_describe(&chain, desc, sizeof desc);
+  const double mp = (double)W * H / 1e6;
+  if (o.json) {
+    printf("{\"input\": \"%s\", \"W\": %d, \"H\": %d, \"C\": %d, \"chain\": \"%s\", \"backend\": \"%s\", "
+           "\"workers\": %d, \"filter_ms\": %.6f, \"total_ms\": %.3f, \"mpix_per_s\": %.1f, "
+           "\"output\": \"%s\"%s%s}\n",
+           source.c_str(), W, H, C, desc, backend.c_str(), n, kernel_ms, total_ms,
+           kernel_ms > 0 ? mp / (kernel_ms / 1e3) : 0.0, outp.c_str(), report[0] ? ", \"runtime\": " : "",
+           report[0] ? report.data() : "");
+  } else {
+    printf("Image properties: W=%d   H=%d   C=%d  (%s)\n", W, H, C, source.c_str());
+    printf("Filter chain:     %s   backend=%s   workers=%d\n", desc, backend.c_str(), n);
+    printf("Process #0 received the gathered image\n");
+    printf("\n______took %.0fns to run modification.\n", kernel_ms * 1e6);
+    printf("______took %.3fms to run modification. (%.1f MP/s; whole call %.1f ms)\n\n", kernel_ms,
+           kernel_ms > 0 ? mp / (kernel_ms / 1e3) : 0.0, total_ms);
+    printf("wrote %s\n", outp.c_str());
+  }
+  b2i_free(img);
+  return 0;
+}

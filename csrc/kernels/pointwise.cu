@@ -1,0 +1,169 @@
+// Streaming kernel for chains without a stencil: [lut] -> [gray] -> [lut] -> [expand].
+//
+// This is what the reference's grayscaleKernel + contrastKernel (kernel.cu:31-58) and the host
+// GRAY2BGR (kernel.cu:210) collapse to when no stencil sits between them: each thread moves
+// 16 pixels with 16-byte loads and stores (3 x LDG.128 -> 1 or 3 x STG.128) instead of three
+// byte loads and one byte store per pixel. The pointers may be peer addresses: reading the band
+// from the owner GPU fuses the scatter (kernel.cu:137), writing into the root GPU's image fuses
+// the gather (kernel.cu:223).
+#include "b200img.h"
+#include "device_utils.cuh"
+#include "tile_plan.hpp"
+
+namespace b2i {
+using namespace dev;
+
+namespace {
+
+constexpr int kPwThreads = 256;
+
+__device__ __forceinline__ uint32_t lut4(const uint8_t* lut, uint32_t w) {
+  const uint32_t a = lut[w & 0xFF], b = lut[(w >> 8) & 0xFF], c = lut[(w >> 16) & 0xFF],
+                 d = lut[w >> 24];
+  return pack4_lo(a, b, c, d);
+}
+
+// 4 gray pixels from 12 interleaved bytes.
+template <int GRAY>
+__device__ __forceinline__ uint32_t gray4(uint32_t w0, uint32_t w1, uint32_t w2,
+                                          const GrayRefCoef& gk, int rgb) {
+  uint32_t g0, g1, g2, g3;
+  if (GRAY == 1) {
+    g0 = gray_ref_f23(byte_to_f23<0>(w0), byte_to_f23<1>(w0), byte_to_f23<2>(w0), gk);
+    g1 = gray_ref_f23(byte_to_f23<3>(w0), byte_to_f23<0>(w1), byte_to_f23<1>(w1), gk);
+    g2 = gray_ref_f23(byte_to_f23<2>(w1), byte_to_f23<3>(w1), byte_to_f23<0>(w2), gk);
+    g3 = gray_ref_f23(byte_to_f23<1>(w2), byte_to_f23<2>(w2), byte_to_f23<3>(w2), gk);
+  } else {
+    g0 = gray_cv_px(w0 & 0xFF, (w0 >> 8) & 0xFF, (w0 >> 16) & 0xFF, rgb);
+    g1 = gray_cv_px(w0 >> 24, w1 & 0xFF, (w1 >> 8) & 0xFF, rgb);
+    g2 = gray_cv_px((w1 >> 16) & 0xFF, w1 >> 24, w2 & 0xFF, rgb);
+    g3 = gray_cv_px((w2 >> 8) & 0xFF, (w2 >> 16) & 0xFF, w2 >> 24, rgb);
+  }
+  return pack4_lo(g0, g1, g2, g3);
+}
+
+// One pixel, any alignment: row tails and images whose pitch is not a multiple of 16.
+template <int CIN, int GRAY, bool EXPAND>
+__device__ __forceinline__ void scalar_px(const PointwiseParams& P, const uint8_t* s, uint8_t* d,
+                                          const uint8_t* lut0, const uint8_t* lut1) {
+  uint32_t v[3];
+#pragma unroll
+  for (int c = 0; c < CIN; ++c) v[c] = P.has_lut0 ? lut0[s[c]] : s[c];
+  if (GRAY) {
+    const int ib = P.rgb_order ? 2 : 0, ir = 2 - ib;
+    uint32_t g = GRAY == 1 ? v[ib] * 11 / 100 + v[1] * 59 / 100 + v[ir] * 3 / 10
+                           : (3735 * v[ib] + 19235 * v[1] + 9798 * v[ir] + 16384) >> 15;
+    if (P.has_lut1) g = lut1[g];
+    if (EXPAND) d[0] = d[1] = d[2] = (uint8_t)g;
+    else d[0] = (uint8_t)g;
+  } else {
+#pragma unroll
+    for (int c = 0; c < CIN; ++c) {
+      const uint32_t o = P.has_lut1 ? lut1[v[c]] : v[c];
+      if (EXPAND) d[0] = d[1] = d[2] = (uint8_t)o;
+      else d[c] = (uint8_t)o;
+    }
+  }
+}
+
+template <int CIN, int GRAY, bool EXPAND>
+__global__ void __launch_bounds__(kPwThreads)
+pointwise_kernel(const __grid_constant__ PointwiseParams P) {
+  __shared__ __align__(16) uint8_t lut0[256];
+  __shared__ __align__(16) uint8_t lut1[256];
+  for (int i = threadIdx.x; i < 64; i += kPwThreads) {
+    reinterpret_cast<uint32_t*>(lut0)[i] = reinterpret_cast<const uint32_t*>(P.lut0)[i];
+    reinterpret_cast<uint32_t*>(lut1)[i] = reinterpret_cast<const uint32_t*>(P.lut1)[i];
+  }
+  __syncthreads();
+  constexpr int COUT = GRAY ? (EXPAND ? 3 : 1) : (EXPAND ? 3 : CIN);
+  constexpr int MID = GRAY ? 1 : CIN;  // channels between the two LUTs
+  const GrayRefCoef gk = gray_ref_coef(P.rgb_order);
+  const int units_x = (P.W + 15) >> 4;  // 16 pixels per unit
+  const long long n_units = (long long)units_x * P.rows;
+  const uint8_t* src = reinterpret_cast<const uint8_t*>(P.src_ptr);
+  uint8_t* dst = reinterpret_cast<uint8_t*>(P.dst_ptr);
+  for (long long u = (long long)blockIdx.x * kPwThreads + threadIdx.x; u < n_units;
+       u += (long long)gridDim.x * kPwThreads) {
+    const int y = (int)(u / units_x), ux = (int)(u - (long long)y * units_x);
+    const int x0 = ux << 4;
+    const uint8_t* s = src + (long long)y * P.src_pitch + (long long)x0 * CIN;
+    uint8_t* d = dst + (long long)y * P.dst_pitch + (long long)x0 * COUT;
+    if (P.vec_ok && x0 + 16 <= P.W) {
+      uint32_t in[4 * CIN];
+#pragma unroll
+      for (int q = 0; q < CIN; ++q) {
+        const uint4 v = ldg_stream_v4(s + 16 * q);
+        in[4 * q] = v.x; in[4 * q + 1] = v.y; in[4 * q + 2] = v.z; in[4 * q + 3] = v.w;
+      }
+      if (P.has_lut0) {
+#pragma unroll
+        for (int q = 0; q < 4 * CIN; ++q) in[q] = lut4(lut0, in[q]);
+      }
+      uint32_t mid[4 * MID];
+      if (GRAY) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) mid[q] = gray4<GRAY ? GRAY : 1>(in[3 * q], in[3 * q + 1], in[3 * q + 2], gk, P.rgb_order);
+      } else {
+#pragma unroll
+        for (int q = 0; q < 4 * MID; ++q) mid[q] = in[q];
+      }
+      if (P.has_lut1) {
+#pragma unroll
+        for (int q = 0; q < 4 * MID; ++q) mid[q] = lut4(lut1, mid[q]);
+      }
+      if (EXPAND) {  // MID == 1: 16 gray bytes -> 48 bytes
+        uint32_t e[12];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          e[3 * q] = __byte_perm(mid[q], 0, 0x1000);
+          e[3 * q + 1] = __byte_perm(mid[q], 0, 0x2211);
+          e[3 * q + 2] = __byte_perm(mid[q], 0, 0x3332);
+        }
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+          stg_stream_v4(d + 16 * q, make_uint4(e[4 * q], e[4 * q + 1], e[4 * q + 2], e[4 * q + 3]));
+      } else {
+#pragma unroll
+        for (int q = 0; q < MID; ++q)
+          stg_stream_v4(d + 16 * q, make_uint4(mid[4 * q], mid[4 * q + 1], mid[4 * q + 2], mid[4 * q + 3]));
+      }
+    } else {
+      const int n = min(16, P.W - x0);
+      for (int i = 0; i < n; ++i)
+        scalar_px<CIN, GRAY, EXPAND>(P, s + i * CIN, d + i * COUT, lut0, lut1);
+    }
+  }
+  // gather completion: the last CTA to finish releases the root's flag
+  if (P.done_flag) {
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t* counters = reinterpret_cast<uint32_t*>(P.counters);
+      if (atomicAdd(&counters[3], 1u) + 1 == gridDim.x) {
+        counters[3] = 0;
+        __threadfence_system();
+        st_release_sys(reinterpret_cast<uint32_t*>(P.done_flag), P.signal_epoch);
+      }
+    }
+  }
+}
+
+}  // namespace
+
+cudaError_t launch_pointwise(const PointwiseParams& P, int grid, cudaStream_t stream) {
+  const int key = P.cin * 100 + P.gray * 10 + (P.expand ? 1 : 0);
+  switch (key) {
+    case 310: pointwise_kernel<3, 1, false><<<grid, kPwThreads, 0, stream>>>(P); break;
+    case 311: pointwise_kernel<3, 1, true><<<grid, kPwThreads, 0, stream>>>(P); break;
+    case 320: pointwise_kernel<3, 2, false><<<grid, kPwThreads, 0, stream>>>(P); break;
+    case 321: pointwise_kernel<3, 2, true><<<grid, kPwThreads, 0, stream>>>(P); break;
+    case 300: pointwise_kernel<3, 0, false><<<grid, kPwThreads, 0, stream>>>(P); break;
+    case 100: pointwise_kernel<1, 0, false><<<grid, kPwThreads, 0, stream>>>(P); break;
+    case 101: pointwise_kernel<1, 0, true><<<grid, kPwThreads, 0, stream>>>(P); break;
+    default: return cudaErrorInvalidValue;
+  }
+  return cudaGetLastError();
+}
+
+}  // namespace b2i

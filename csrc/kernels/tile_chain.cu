@@ -1,0 +1,585 @@
+// The tile-chain kernel: one persistent sm_100a kernel that runs a whole filter-chain segment
+// per tile in shared memory.
+//
+//   global --TMA(UTMALDG)--> raw tile --phase 0..n-1 (smem -> smem)--> staging --TMA(UTMASTG)--> global
+//
+// It replaces the reference's grayscaleKernel / contrastKernel / embossKernel launches and the
+// host-side GRAY2BGR (kernel.cu:31-94,192-195,210) by one pass over HBM: 3 B/px in, 3 B/px out
+// instead of 8 B/px of device traffic plus a D2H copy and a host expand. The source and the
+// destination are "views" that may live on another GPU (peer-mapped or IPC-mapped memory), which
+// is how scatter (kernel.cu:137), the halo exchange the reference lacks, and gather
+// (kernel.cu:223) are fused into this kernel instead of being separate transfers:
+//   * scatter : the source tensor map points at the owner GPU's image, tiles are TMA-loaded
+//               across NVLink;
+//   * halo    : boundary tiles are additionally stored into the neighbours' ghost rows, then a
+//               system-scope flag is released; consumers acquire it before loading ghost rows;
+//   * gather  : the destination tensor map points into the root GPU's output image.
+#include "b200img.h"
+#include "device_utils.cuh"
+#include "tile_plan.hpp"
+
+namespace b2i {
+using namespace dev;
+
+namespace {
+
+struct Tile {
+  int tx0, ty0;  // global pixel coordinates of the tile's first output pixel
+  bool edge;     // some plane cell of this tile lies outside the image
+  bool first_row, last_row;
+};
+
+__device__ __forceinline__ Tile tile_of(const TileParams& P, int t) {
+  // Boundary-first order: the first and the last tile row of a band are produced first so that
+  // their halo pushes reach the neighbours early.
+  int trow = t / P.tiles_x, tcol = t - trow * P.tiles_x;
+  if (P.push_rows > 0 && P.tiles_y > 2) {
+    if (trow == 1) trow = P.tiles_y - 1;
+    else if (trow > 1) trow -= 1;
+  }
+  Tile T;
+  T.tx0 = tcol * kTileW;
+  T.ty0 = P.y0 + trow * P.th;
+  T.first_row = trow == 0;
+  T.last_row = trow == P.tiles_y - 1;
+  const int R = P.halo;
+  T.edge = T.tx0 - kApron < 0 || T.tx0 + kTileW + kApron > P.W || T.ty0 - R < 0 ||
+           T.ty0 + P.th + R + kRowGroup > P.H;
+  return T;
+}
+
+// ---- tile input -------------------------------------------------------------------------------
+
+// Fallback loader for sources TMA cannot describe (pitch or base not 16-byte aligned): every
+// thread copies words, zero-filling what lies outside the view, exactly like TMA's OOB fill.
+__device__ void load_tile_generic(const TileParams& P, const Tile& T, uint8_t* raw) {
+  const int pitch = P.buf[BUF_RAW].pitch, words = pitch >> 2;
+  const int64_t xb0 = (int64_t)(T.tx0 - kApron) * P.cin;
+  const int64_t row_bytes = (int64_t)P.W * P.cin;
+  const uint8_t* src = reinterpret_cast<const uint8_t*>(P.src_ptr);
+  for (int idx = threadIdx.x; idx < words * P.raw_rows; idx += kTileThreads) {
+    const int pr = idx / words, w = idx - pr * words;
+    const int gy = T.ty0 - P.halo + pr;
+    const int64_t xb = xb0 + 4 * w;
+    uint32_t v = 0;
+    if (gy >= P.src_y_begin && gy < P.src_y_end && xb + 3 >= 0 && xb < row_bytes) {
+      const uint8_t* p = src + (int64_t)(gy - P.src_y_begin) * P.src_pitch + xb;
+      if (xb >= 0 && xb + 3 < row_bytes && (reinterpret_cast<uintptr_t>(p) & 3) == 0) {
+        v = *reinterpret_cast<const uint32_t*>(p);
+      } else {
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+          if (xb + b >= 0 && xb + b < row_bytes) v |= (uint32_t)p[b] << (8 * b);
+      }
+    }
+    *reinterpret_cast<uint32_t*>(raw + (size_t)pr * pitch + 4 * w) = v;
+  }
+}
+
+// Paints the border rule of the next stencil onto the cells of `plane` that lie outside the
+// image (edge tiles only). Sources are in-image cells of the same plane, which this never writes.
+__device__ void fix_border(const TileParams& P, const Tile& T, uint8_t* plane, int pitch, int C,
+                           int margin, int border) {
+  const int R = P.halo;
+  const int rows = P.th + 2 * margin, cols = kTileW + 2 * margin;
+  for (int idx = threadIdx.x; idx < rows * cols; idx += kTileThreads) {
+    const int rr = idx / cols, cc = idx - rr * cols;
+    const int pr = R - margin + rr, pc = kApron - margin + cc;
+    const int gx = T.tx0 - kApron + pc, gy = T.ty0 - R + pr;
+    if ((unsigned)gx < (unsigned)P.W && (unsigned)gy < (unsigned)P.H) continue;
+    uint8_t* d = plane + (size_t)pr * pitch + pc * C;
+    if (border == B2I_BORDER_ZERO) {
+      for (int c = 0; c < C; ++c) d[c] = 0;
+      continue;
+    }
+    int sx = gx, sy = gy;
+    if (border == B2I_BORDER_REFLECT101) {
+      sx = sx < 0 ? -sx : (sx >= P.W ? 2 * P.W - 2 - sx : sx);
+      sy = sy < 0 ? -sy : (sy >= P.H ? 2 * P.H - 2 - sy : sy);
+    } else {  // replicate
+      sx = min(max(sx, 0), P.W - 1);
+      sy = min(max(sy, 0), P.H - 1);
+    }
+    const int spr = sy - (T.ty0 - R), spc = sx - (T.tx0 - kApron);
+    // sources outside this tile's planes belong to cells no valid output depends on
+    if (spr < 0 || spr >= P.th + 2 * R || spc < 0 || spc >= kPlaneW) continue;
+    const uint8_t* s = plane + (size_t)spr * pitch + spc * C;
+    for (int c = 0; c < C; ++c) d[c] = s[c];
+  }
+}
+
+// ---- pointwise phases (smem -> smem) ------------------------------------------------------------
+
+__device__ __forceinline__ uint32_t lut4(const uint8_t* lut, uint32_t w) {
+  const uint32_t a = lut[w & 0xFF], b = lut[(w >> 8) & 0xFF], c = lut[(w >> 16) & 0xFF],
+                 d = lut[w >> 24];
+  return pack4_lo(a, b, c, d);
+}
+
+template <int TYPE>
+__device__ void pw_phase(const TileParams& P, const PhaseDesc& ph, uint8_t* sbase, int spitch,
+                         int sxorg, int syorg, uint8_t* dbase, int dpitch, int dxorg, int dyorg,
+                         const uint8_t* lut) {
+  const int R = P.halo, m = ph.margin, mc = m > 0 ? kApron : 0;
+  const int ux = (kTileW + 2 * mc) >> 2;  // units of 4 pixels per row
+  const int rows = P.th + 2 * m;
+  const GrayRefCoef gk = gray_ref_coef(P.rgb_order);
+  for (int idx = threadIdx.x; idx < ux * rows; idx += kTileThreads) {
+    const int rr = idx / ux, u = idx - rr * ux;
+    const int pr = R - m + rr, pc = kApron - mc + 4 * u;
+    const uint8_t* s = sbase + (size_t)(pr - syorg) * spitch + (pc - sxorg) * ph.cin;
+    uint8_t* d = dbase + (size_t)(pr - dyorg) * dpitch + (pc - dxorg) * ph.cout;
+    if (TYPE == PH_GRAY_REF || TYPE == PH_GRAY_CV) {
+      const uint32_t w0 = reinterpret_cast<const uint32_t*>(s)[0],
+                     w1 = reinterpret_cast<const uint32_t*>(s)[1],
+                     w2 = reinterpret_cast<const uint32_t*>(s)[2];
+      uint32_t g0, g1, g2, g3;
+      if (TYPE == PH_GRAY_REF) {
+        g0 = gray_ref_f23(byte_to_f23<0>(w0), byte_to_f23<1>(w0), byte_to_f23<2>(w0), gk);
+        g1 = gray_ref_f23(byte_to_f23<3>(w0), byte_to_f23<0>(w1), byte_to_f23<1>(w1), gk);
+        g2 = gray_ref_f23(byte_to_f23<2>(w1), byte_to_f23<3>(w1), byte_to_f23<0>(w2), gk);
+        g3 = gray_ref_f23(byte_to_f23<1>(w2), byte_to_f23<2>(w2), byte_to_f23<3>(w2), gk);
+      } else {
+        g0 = gray_cv_px(w0 & 0xFF, (w0 >> 8) & 0xFF, (w0 >> 16) & 0xFF, P.rgb_order);
+        g1 = gray_cv_px(w0 >> 24, w1 & 0xFF, (w1 >> 8) & 0xFF, P.rgb_order);
+        g2 = gray_cv_px((w1 >> 16) & 0xFF, w1 >> 24, w2 & 0xFF, P.rgb_order);
+        g3 = gray_cv_px((w2 >> 8) & 0xFF, (w2 >> 16) & 0xFF, w2 >> 24, P.rgb_order);
+      }
+      if (lut) {
+        g0 = lut[g0 & 0xFF];
+        g1 = lut[g1 & 0xFF];
+        g2 = lut[g2 & 0xFF];
+        g3 = lut[g3 & 0xFF];
+      }
+      *reinterpret_cast<uint32_t*>(d) = pack4_lo(g0, g1, g2, g3);
+    } else if (TYPE == PH_COPY) {
+      for (int c = 0; c < ph.cin; ++c) {
+        uint32_t w = reinterpret_cast<const uint32_t*>(s)[c];
+        if (lut) w = lut4(lut, w);
+        reinterpret_cast<uint32_t*>(d)[c] = w;
+      }
+    } else {  // PH_EXPAND
+      uint32_t w = reinterpret_cast<const uint32_t*>(s)[0];
+      if (lut) w = lut4(lut, w);
+      reinterpret_cast<uint32_t*>(d)[0] = __byte_perm(w, 0, 0x1000);
+      reinterpret_cast<uint32_t*>(d)[1] = __byte_perm(w, 0, 0x2211);
+      reinterpret_cast<uint32_t*>(d)[2] = __byte_perm(w, 0, 0x3332);
+    }
+  }
+}
+
+// ---- stencil phases (smem -> smem) ----------------------------------------------------------------
+
+// Bytes [o, o+4) of the 24-byte row window a[0..5].
+template <int O>
+__device__ __forceinline__ uint32_t window(const uint32_t (&a)[6]) {
+  static_assert(O >= 0 && O <= 20, "dp4a window outside the row registers");
+  if constexpr ((O & 3) == 0) return a[O >> 2];
+  else return __funnelshift_r(a[O >> 2], a[(O >> 2) + 1], (O & 3) * 8);
+}
+
+// dp4a window offsets (relative to the output byte) per (channels, ksize): see plan.cpp.
+template <int C, int K, int D>
+struct DpOff {
+  static constexpr int value = C == 1 ? (K == 3 ? -1 : (D == 0 ? -2 : 2))
+                                      : (K == 3 ? (D == 0 ? -3 : 0) : (D == 0 ? -6 : (D == 1 ? 0 : 3)));
+};
+template <int C, int K>
+struct DpCount {
+  static constexpr int value = C == 1 ? (K == 3 ? 1 : 2) : (K == 3 ? 2 : 3);
+};
+
+template <int C, int K, bool SOBEL, int I, int D>
+__device__ __forceinline__ void tap_one(const uint32_t (&a)[6], const uint32_t* w,
+                                        const uint32_t* w2, int& acc, int& acc2) {
+  constexpr int O = I + 8 + DpOff<C, K, D>::value;
+  const uint32_t v = window<O>(a);
+  acc = dp4a_us(v, w[D], acc);
+  if (SOBEL) acc2 = dp4a_us(v, w2[D], acc2);
+}
+template <int C, int K, bool SOBEL, int I>
+__device__ __forceinline__ void tap_px(const uint32_t (&a)[6], const uint32_t* w,
+                                       const uint32_t* w2, int& acc, int& acc2) {
+  tap_one<C, K, SOBEL, I, 0>(a, w, w2, acc, acc2);
+  if constexpr (DpCount<C, K>::value > 1) tap_one<C, K, SOBEL, I, 1>(a, w, w2, acc, acc2);
+  if constexpr (DpCount<C, K>::value > 2) tap_one<C, K, SOBEL, I, 2>(a, w, w2, acc, acc2);
+}
+template <int C, int K, bool SOBEL>
+__device__ __forceinline__ void tap_row(const uint32_t (&a)[6], const uint32_t* w,
+                                        const uint32_t* w2, int (&acc)[8], int (&acc2)[8]) {
+  tap_px<C, K, SOBEL, 0>(a, w, w2, acc[0], acc2[0]);
+  tap_px<C, K, SOBEL, 1>(a, w, w2, acc[1], acc2[1]);
+  tap_px<C, K, SOBEL, 2>(a, w, w2, acc[2], acc2[2]);
+  tap_px<C, K, SOBEL, 3>(a, w, w2, acc[3], acc2[3]);
+  tap_px<C, K, SOBEL, 4>(a, w, w2, acc[4], acc2[4]);
+  tap_px<C, K, SOBEL, 5>(a, w, w2, acc[5], acc2[5]);
+  tap_px<C, K, SOBEL, 6>(a, w, w2, acc[6], acc2[6]);
+  tap_px<C, K, SOBEL, 7>(a, w, w2, acc[7], acc2[7]);
+}
+
+// One thread: an 8-byte-wide strip, kRowGroup output rows, K + kRowGroup - 1 input rows each
+// read once (three LDS.64), all taps through dp4a.
+template <int C, int K, bool SOBEL>
+__device__ void stencil_phase(const TileParams& P, const PhaseDesc& ph, const Tile& T,
+                              const uint8_t* sbase, int spitch, uint8_t* dbase, int dpitch,
+                              int dxorg, int dyorg, const uint8_t* lut) {
+  constexpr int r = K / 2;
+  constexpr int RG = SOBEL ? 2 : kRowGroup;
+  const int R = P.halo, m = ph.margin, mc = m > 0 ? kApron : 0;
+  const int strips = ((kTileW + 2 * mc) * C) >> 3;
+  const int rows = P.th + 2 * m;
+  const int groups = (rows + RG - 1) / RG;
+  const bool ref = ph.border == B2I_BORDER_REF;
+  const bool scale = (ph.shift | ph.bias) != 0;
+  for (int item = threadIdx.x; item < strips * groups; item += kTileThreads) {
+    const int g = item / strips, strip = item - g * strips;
+    const int bc = (kApron - mc) * C + strip * 8;  // plane byte column of the strip
+    const int pr0 = R - m + g * RG;                 // plane row of the first output row
+    int acc[RG][8], acc2[SOBEL ? RG : 1][8];
+    uint32_t centre[RG][2];
+#pragma unroll
+    for (int o = 0; o < RG; ++o)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        acc[o][i] = 0;
+        if (SOBEL) acc2[o][i] = 0;
+      }
+    const uint8_t* srow = sbase + (size_t)(pr0 - r) * spitch + bc - 8;
+#pragma unroll
+    for (int j = 0; j < K + RG - 1; ++j) {
+      uint32_t a[6];
+      const uint2 v0 = *reinterpret_cast<const uint2*>(srow + (size_t)j * spitch);
+      const uint2 v1 = *reinterpret_cast<const uint2*>(srow + (size_t)j * spitch + 8);
+      const uint2 v2 = *reinterpret_cast<const uint2*>(srow + (size_t)j * spitch + 16);
+      a[0] = v0.x; a[1] = v0.y; a[2] = v1.x; a[3] = v1.y; a[4] = v2.x; a[5] = v2.y;
+#pragma unroll
+      for (int o = 0; o < RG; ++o) {
+        const int k = j - o;  // stencil row this input row is for output row o
+        if (k < 0 || k >= K) continue;
+        if (k == r) {
+          centre[o][0] = a[2];
+          centre[o][1] = a[3];
+        }
+        if (SOBEL) {
+          tap_row<C, K, true>(a, ph.wpk[k], ph.wpk2[k], acc[o], acc2[o]);
+        } else {
+          // rows of zero weights (emboss5 has one tap per row, the 3x3 kernels none) are skipped
+          if ((ph.wpk[k][0] | ph.wpk[k][1] | ph.wpk[k][2]) != 0)
+            tap_row<C, K, false>(a, ph.wpk[k], ph.wpk[k], acc[o], acc[o]);
+        }
+      }
+    }
+    // REF border: only pixels x in [r+1, W-r-1], y in [r+1, H-r-1] are filtered (kernel.cu:83,
+    // restricted to its well-defined part); everything else passes the input through.
+    uint32_t m0 = 0xFFFFFFFFu, m1 = 0xFFFFFFFFu;
+    if (ref) {
+      const int gxb0 = (T.tx0 - kApron) * C + bc;
+      const int lo = (r + 1) * C - gxb0, hi = (P.W - r) * C - 1 - gxb0;
+      if (lo > 0 || hi < 7) {
+        m0 = m1 = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          if (i >= lo && i <= hi) m0 |= 0xFFu << (8 * i);
+          if (i + 4 >= lo && i + 4 <= hi) m1 |= 0xFFu << (8 * i);
+        }
+      }
+    }
+#pragma unroll
+    for (int o = 0; o < RG; ++o) {
+      const int pr = pr0 + o;
+      if (pr >= R - m + rows) break;
+      if (SOBEL) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[o][i] = abs(acc[o][i]) + abs(acc2[o][i]);
+      } else if (scale) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[o][i] = (acc[o][i] + ph.bias) >> ph.shift;
+      }
+      uint32_t r0 = sat_pack4(acc[o][0], acc[o][1], acc[o][2], acc[o][3]);
+      uint32_t r1 = sat_pack4(acc[o][4], acc[o][5], acc[o][6], acc[o][7]);
+      if (ref) {
+        const int gy = T.ty0 - R + pr;
+        const bool row_ok = gy >= r + 1 && gy <= P.H - r - 1;
+        const uint32_t mm0 = row_ok ? m0 : 0u, mm1 = row_ok ? m1 : 0u;
+        r0 = (r0 & mm0) | (centre[o][0] & ~mm0);
+        r1 = (r1 & mm1) | (centre[o][1] & ~mm1);
+      }
+      if (lut) {
+        r0 = lut4(lut, r0);
+        r1 = lut4(lut, r1);
+      }
+      if (ph.expand) {  // C == 1: 8 gray pixels -> 24 bytes of BGR (kernel.cu:210 fused here)
+        uint8_t* d = dbase + (size_t)(pr - dyorg) * dpitch + (bc - dxorg) * 3;
+        uint2 e0, e1, e2;
+        e0.x = __byte_perm(r0, 0, 0x1000);
+        e0.y = __byte_perm(r0, 0, 0x2211);
+        e1.x = __byte_perm(r0, 0, 0x3332);
+        e1.y = __byte_perm(r1, 0, 0x1000);
+        e2.x = __byte_perm(r1, 0, 0x2211);
+        e2.y = __byte_perm(r1, 0, 0x3332);
+        reinterpret_cast<uint2*>(d)[0] = e0;
+        reinterpret_cast<uint2*>(d)[1] = e1;
+        reinterpret_cast<uint2*>(d)[2] = e2;
+      } else {
+        uint8_t* d = dbase + (size_t)(pr - dyorg) * dpitch + (bc - dxorg * C);
+        *reinterpret_cast<uint2*>(d) = make_uint2(r0, r1);
+      }
+    }
+  }
+}
+
+// ---- tile output --------------------------------------------------------------------------------
+
+// Fallback for destinations TMA cannot describe. Rows outside [row_lo, row_hi) and pixels at
+// or beyond W are dropped, like TMA's clipping.
+__device__ void store_tile_generic(const TileParams& P, const Tile& T, const uint8_t* stage,
+                                   uint64_t dst_ptr, int64_t dst_pitch, int dst_y_begin,
+                                   int row_lo, int row_hi) {
+  const int pitch = P.buf[BUF_STAGE].pitch, words = pitch >> 2;
+  const int64_t row_bytes = (int64_t)P.W * P.cout;
+  const int64_t xb0 = (int64_t)T.tx0 * P.cout;
+  uint8_t* dst = reinterpret_cast<uint8_t*>(dst_ptr);
+  for (int idx = threadIdx.x; idx < words * P.th; idx += kTileThreads) {
+    const int rr = idx / words, w = idx - rr * words;
+    const int gy = T.ty0 + rr;
+    const int64_t xb = xb0 + 4 * w;
+    if (gy < row_lo || gy >= row_hi || xb >= row_bytes) continue;
+    const uint32_t v = *reinterpret_cast<const uint32_t*>(stage + (size_t)rr * pitch + 4 * w);
+    uint8_t* p = dst + (int64_t)(gy - dst_y_begin) * dst_pitch + xb;
+    if (xb + 3 < row_bytes && (reinterpret_cast<uintptr_t>(p) & 3) == 0) {
+      *reinterpret_cast<uint32_t*>(p) = v;
+    } else {
+      for (int b = 0; b < 4 && xb + b < row_bytes; ++b) p[b] = (uint8_t)(v >> (8 * b));
+    }
+  }
+}
+
+}  // namespace
+
+// ---- the kernel -----------------------------------------------------------------------------------
+
+__global__ void __launch_bounds__(kTileThreads, 2)
+tile_chain_kernel(const __grid_constant__ TileParams P, const __grid_constant__ CUtensorMap src_map,
+                  const __grid_constant__ CUtensorMap dst_map,
+                  const __grid_constant__ CUtensorMap push_up_map,
+                  const __grid_constant__ CUtensorMap push_dn_map) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + P.bar_off);
+  uint8_t* luts = smem + P.lut_off;
+  const int tid = threadIdx.x;
+
+  if (tid == 0) {
+    mbar_init(&full_bar[0], 1);
+    mbar_init(&full_bar[1], 1);
+    fence_mbar_init();
+    if (P.use_tma_load) tma_prefetch_desc(&src_map);
+    if (P.use_tma_store) tma_prefetch_desc(&dst_map);
+  }
+  for (int i = tid; i < kMaxLuts * 256 / 4; i += kTileThreads)
+    reinterpret_cast<uint32_t*>(luts)[i] = reinterpret_cast<const uint32_t*>(&P.luts[0][0])[i];
+  __syncthreads();
+
+  uint32_t* counters = reinterpret_cast<uint32_t*>(P.counters);
+  uint32_t* status = reinterpret_cast<uint32_t*>(P.status);
+  const int push_tile_rows = P.push_rows > 0 ? (P.push_rows + P.th - 1) / P.th : 0;
+
+  // Thread 0: make sure the neighbours' halo rows for this tile have landed in our ghost rows
+  // (acquire their flag), then start the TMA load of the tile into stage `s`.
+  auto issue_load = [&](int t, int s) {
+    const Tile T = tile_of(P, t);
+    if (P.wait_up_flag && T.ty0 - P.halo < P.y0) {
+      if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_up_flag), P.wait_epoch, P.timeout_ns))
+        atomicExch(status, 1u);
+      asm volatile("fence.proxy.async;" ::: "memory");
+    }
+    if (P.wait_dn_flag && T.ty0 + P.th + P.halo > P.y1) {
+      if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_dn_flag), P.wait_epoch, P.timeout_ns))
+        atomicExch(status, 2u);
+      asm volatile("fence.proxy.async;" ::: "memory");
+    }
+    if (P.use_tma_load) {
+      fence_proxy_async_smem();  // earlier generic-proxy writes to this stage (border fix-up)
+      mbar_arrive_expect_tx(&full_bar[s], (uint32_t)P.raw_tx_bytes);
+      tma_load_2d(smem + P.buf[BUF_RAW].off + s * P.raw_stage_bytes, &src_map,
+                  ((T.tx0 - kApron) * P.cin) >> 2, T.ty0 - P.halo - P.src_y_begin, &full_bar[s]);
+    }
+  };
+
+  int it = 0;
+  bool store_pending = false;
+  Tile prevT = tile_of(P, 0);
+  if (tid == 0 && (int)blockIdx.x < P.n_tiles) issue_load(blockIdx.x, 0);
+  if (!P.use_tma_load) __syncthreads();  // the flag acquire of thread 0 orders everyone's loads
+
+  for (int t = blockIdx.x; t < P.n_tiles; t += gridDim.x, ++it) {
+    const int s = it & 1;
+    const Tile T = tile_of(P, t);
+    uint8_t* raw = smem + P.buf[BUF_RAW].off + s * P.raw_stage_bytes;
+    const int tn = t + gridDim.x;
+    if (tid == 0 && tn < P.n_tiles) issue_load(tn, s ^ 1);  // stage s^1 was released by the
+                                                             // barrier ending the previous tile
+    if (P.use_tma_load) {
+      mbar_wait(&full_bar[s], (it >> 1) & 1);
+    } else {
+      load_tile_generic(P, T, raw);
+      __syncthreads();
+    }
+    if (P.raw_fix_border >= 0 && T.edge) {
+      fix_border(P, T, raw, P.buf[BUF_RAW].pitch, P.cin, P.halo, P.raw_fix_border);
+      __syncthreads();
+    }
+
+    for (int k = 0; k < P.n_phases; ++k) {
+      const PhaseDesc& ph = P.ph[k];
+      const BufDesc& sb = P.buf[ph.src];
+      const BufDesc& db = P.buf[ph.dst];
+      uint8_t* sbase = ph.src == BUF_RAW ? raw : smem + sb.off;
+      uint8_t* dbase = smem + db.off;
+      const uint8_t* lut = ph.lut >= 0 ? luts + 256 * ph.lut : nullptr;
+      if (ph.dst == BUF_STAGE && store_pending) {
+        // the previous tile's TMA store must have drained the staging tile before it is reused;
+        // waiting for full completion here also lets thread 0 publish that tile's flags
+        if (tid == 0) {
+          tma_store_wait_all();
+          if (P.signal_up_flag || P.signal_dn_flag || P.done_flag) {
+            asm volatile("fence.proxy.async;" ::: "memory");
+            __threadfence_system();
+            const int n_push = push_tile_rows * P.tiles_x;
+            if (P.signal_up_flag && prevT.ty0 < P.y0 + P.push_rows)
+              if (atomicAdd(&counters[0], 1u) + 1 == (uint32_t)n_push) {
+                counters[0] = 0;
+                st_release_sys(reinterpret_cast<uint32_t*>(P.signal_up_flag), P.signal_epoch);
+              }
+            if (P.signal_dn_flag && prevT.ty0 + P.th > P.y1 - P.push_rows)
+              if (atomicAdd(&counters[1], 1u) + 1 == (uint32_t)n_push) {
+                counters[1] = 0;
+                st_release_sys(reinterpret_cast<uint32_t*>(P.signal_dn_flag), P.signal_epoch);
+              }
+            if (P.done_flag)
+              if (atomicAdd(&counters[2], 1u) + 1 == (uint32_t)P.n_tiles) {
+                counters[2] = 0;
+                st_release_sys(reinterpret_cast<uint32_t*>(P.done_flag), P.signal_epoch);
+              }
+          }
+        }
+        __syncthreads();
+        store_pending = false;
+      }
+      switch (ph.type) {
+        case PH_GRAY_REF:
+          pw_phase<PH_GRAY_REF>(P, ph, sbase, sb.pitch, sb.xorg, sb.yorg, dbase, db.pitch, db.xorg, db.yorg, lut);
+          break;
+        case PH_GRAY_CV:
+          pw_phase<PH_GRAY_CV>(P, ph, sbase, sb.pitch, sb.xorg, sb.yorg, dbase, db.pitch, db.xorg, db.yorg, lut);
+          break;
+        case PH_COPY:
+          pw_phase<PH_COPY>(P, ph, sbase, sb.pitch, sb.xorg, sb.yorg, dbase, db.pitch, db.xorg, db.yorg, lut);
+          break;
+        case PH_EXPAND:
+          pw_phase<PH_EXPAND>(P, ph, sbase, sb.pitch, sb.xorg, sb.yorg, dbase, db.pitch, db.xorg, db.yorg, lut);
+          break;
+        case PH_SOBEL:
+          if (ph.cin == 1) stencil_phase<1, 3, true>(P, ph, T, sbase, sb.pitch, dbase, db.pitch, db.xorg, db.yorg, lut);
+          else stencil_phase<3, 3, true>(P, ph, T, sbase, sb.pitch, dbase, db.pitch, db.xorg, db.yorg, lut);
+          break;
+        default:
+          if (ph.cin == 1) {
+            if (ph.ksize == 3) stencil_phase<1, 3, false>(P, ph, T, sbase, sb.pitch, dbase, db.pitch, db.xorg, db.yorg, lut);
+            else stencil_phase<1, 5, false>(P, ph, T, sbase, sb.pitch, dbase, db.pitch, db.xorg, db.yorg, lut);
+          } else {
+            if (ph.ksize == 3) stencil_phase<3, 3, false>(P, ph, T, sbase, sb.pitch, dbase, db.pitch, db.xorg, db.yorg, lut);
+            else stencil_phase<3, 5, false>(P, ph, T, sbase, sb.pitch, dbase, db.pitch, db.xorg, db.yorg, lut);
+          }
+          break;
+      }
+      if (ph.dst == BUF_STAGE && P.use_tma_store) fence_proxy_async_smem();
+      __syncthreads();
+      if (ph.fix_border >= 0 && T.edge) {
+        fix_border(P, T, dbase, db.pitch, ph.cout, ph.margin, ph.fix_border);
+        __syncthreads();
+      }
+    }
+
+    // ---- tile output: own rows, plus the halo rows pushed into the neighbours' ghost rows ----
+    const uint8_t* stage = smem + P.buf[BUF_STAGE].off;
+    const bool push_up = P.push_up_ptr && T.ty0 < P.y0 + P.push_rows;
+    const bool push_dn = P.push_dn_ptr && T.ty0 + P.th > P.y1 - P.push_rows;
+    if (P.use_tma_store) {
+      if (tid == 0) {
+        const int xw = (T.tx0 * P.cout) >> 2;
+        tma_store_2d(&dst_map, xw, T.ty0 - P.dst_y_begin, stage);
+        if (push_up) tma_store_2d(&push_up_map, xw, T.ty0 - P.push_up_y_begin, stage);
+        if (push_dn) tma_store_2d(&push_dn_map, xw, T.ty0 - P.push_dn_y_begin, stage);
+        tma_store_commit();
+      }
+    } else {
+      store_tile_generic(P, T, stage, P.dst_ptr, P.dst_pitch, P.dst_y_begin,
+                         max(P.y0, P.dst_y_begin), min(P.y1, P.dst_y_end));
+      if (push_up)
+        store_tile_generic(P, T, stage, P.push_up_ptr, P.push_pitch, P.push_up_y_begin, P.y0,
+                           P.y0 + P.push_rows);
+      if (push_dn)
+        store_tile_generic(P, T, stage, P.push_dn_ptr, P.push_pitch, P.push_dn_y_begin,
+                           P.y1 - P.push_rows, P.y1);
+    }
+    if (!P.use_tma_store && (P.signal_up_flag || P.signal_dn_flag || P.done_flag))
+      __threadfence_system();  // plain stores: make them visible before thread 0 publishes flags
+    store_pending = true;
+    prevT = T;
+    // every thread is past its reads of `raw` (stage s) here: the next iteration may refill it
+    __syncthreads();
+  }
+
+  // drain: the last tile's stores, then its flags
+  if (tid == 0 && store_pending) {
+    if (P.use_tma_store) tma_store_wait_all();
+    if (P.signal_up_flag || P.signal_dn_flag || P.done_flag) {
+      asm volatile("fence.proxy.async;" ::: "memory");
+      __threadfence_system();
+      const int n_push = push_tile_rows * P.tiles_x;
+      if (P.signal_up_flag && prevT.ty0 < P.y0 + P.push_rows)
+        if (atomicAdd(&counters[0], 1u) + 1 == (uint32_t)n_push) {
+          counters[0] = 0;
+          st_release_sys(reinterpret_cast<uint32_t*>(P.signal_up_flag), P.signal_epoch);
+        }
+      if (P.signal_dn_flag && prevT.ty0 + P.th > P.y1 - P.push_rows)
+        if (atomicAdd(&counters[1], 1u) + 1 == (uint32_t)n_push) {
+          counters[1] = 0;
+          st_release_sys(reinterpret_cast<uint32_t*>(P.signal_dn_flag), P.signal_epoch);
+        }
+      if (P.done_flag)
+        if (atomicAdd(&counters[2], 1u) + 1 == (uint32_t)P.n_tiles) {
+          counters[2] = 0;
+          st_release_sys(reinterpret_cast<uint32_t*>(P.done_flag), P.signal_epoch);
+        }
+    }
+  }
+}
+
+cudaError_t launch_tile_chain(const TileParams& P, const CUtensorMap& src_map,
+                              const CUtensorMap& dst_map, const CUtensorMap& push_up_map,
+                              const CUtensorMap& push_dn_map, int grid, cudaStream_t stream) {
+  static thread_local int configured_smem[64] = {0};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 64 && configured_smem[dev] < P.smem_bytes) {
+    e = cudaFuncSetAttribute(tile_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             P.smem_bytes);
+    if (e != cudaSuccess) return e;
+    configured_smem[dev] = P.smem_bytes;
+  }
+  tile_chain_kernel<<<grid, kTileThreads, P.smem_bytes, stream>>>(P, src_map, dst_map, push_up_map,
+                                                                  push_dn_map);
+  return cudaGetLastError();
+}
+
+cudaError_t tile_chain_occupancy(int smem_bytes, int* blocks_per_sm) {
+  cudaError_t e = cudaFuncSetAttribute(tile_chain_kernel,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+  if (e != cudaSuccess) return e;
+  return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, tile_chain_kernel,
+                                                       kTileThreads, smem_bytes);
+}
+
+}  // namespace b2i

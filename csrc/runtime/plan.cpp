@@ -1,0 +1,693 @@
+// Chain -> plan compiler and the band-launch entry point.
+//
+// The reference has no such layer: its pipeline is three literal kernel launches
+// (kernel.cu:192-195). Here a chain is compiled once into segments; each segment is one launch
+// of either the streaming pointwise kernel (kernels/pointwise.cu) or the tile-chain kernel
+// (kernels/tile_chain.cu). Compilation folds every run of u8->u8 pointwise ops into one LUT,
+// attaches LUTs and the gray->BGR expand to the neighbouring stencil, lowers stencil weights to
+// packed dp4a operands and lays out shared memory for a tile height chosen per launch.
+#include <cuda.h>
+#include <cudaTypedefs.h>
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "../core/error.hpp"
+#include "../kernels/tile_plan.hpp"
+
+namespace b2i {
+cudaError_t launch_tile_chain(const TileParams& P, const CUtensorMap& src_map,
+                              const CUtensorMap& dst_map, const CUtensorMap& push_up_map,
+                              const CUtensorMap& push_dn_map, int grid, cudaStream_t stream);
+cudaError_t tile_chain_occupancy(int smem_bytes, int* blocks_per_sm);
+cudaError_t launch_pointwise(const PointwiseParams& P, int grid, cudaStream_t stream);
+int run_naive(const b2i_chain_t* chain, const uint8_t* src, int W, int H, int C, size_t src_pitch,
+              uint8_t* dst, size_t dst_pitch, uint8_t* tmp0, uint8_t* tmp1, uint8_t* lut_scratch,
+              cudaStream_t stream);
+}  // namespace b2i
+
+#define B2I_CUDA(expr)                                                                  \
+  do {                                                                                  \
+    cudaError_t e_ = (expr);                                                            \
+    if (e_ != cudaSuccess)                                                              \
+      B2I_FAIL(e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver             \
+                   ? B2I_ERR_NO_DEVICE                                                  \
+                   : B2I_ERR_CUDA,                                                      \
+               "%s: %s", #expr, cudaGetErrorString(e_));                                \
+  } while (0)
+
+using namespace b2i;
+
+namespace {
+
+struct Segment {
+  bool pointwise = false;
+  int cin = 0, cout = 0, halo = 0;
+  // tile segments
+  std::vector<PhaseDesc> phases;
+  int n_luts = 0;
+  uint8_t luts[kMaxLuts][256];
+  int raw_fix_border = -1;
+  int chan_a = 0, chan_b = 0;  // widest plane each ping-pong buffer has to hold
+  // pointwise segments
+  int pw_gray = 0, pw_expand = 0, pw_has_lut0 = 0, pw_has_lut1 = 0;
+  uint8_t pw_lut0[256], pw_lut1[256];
+};
+
+// A chain element after LUT folding.
+struct Elem {
+  int kind;  // b2i_opkind
+  const b2i_op_t* op;
+  uint8_t lut[256];
+};
+
+void compose_lut(uint8_t* first_then, const uint8_t* second) {  // first_then := second o first
+  for (int v = 0; v < 256; ++v) first_then[v] = second[first_then[v]];
+}
+
+uint32_t pack_w(int a, int b, int c, int d) {
+  return (uint32_t)(uint8_t)(int8_t)a | ((uint32_t)(uint8_t)(int8_t)b << 8) |
+         ((uint32_t)(uint8_t)(int8_t)c << 16) | ((uint32_t)(uint8_t)(int8_t)d << 24);
+}
+
+// dp4a operand layout per (channels, ksize); must match DpOff/DpCount in tile_chain.cu.
+void pack_rows(int C, int K, const int* w /*K*K*/, uint32_t out[5][3]) {
+  memset(out, 0, sizeof(uint32_t) * 15);
+  for (int j = 0; j < K; ++j) {
+    const int* r = w + j * K;
+    if (C == 1 && K == 3) {
+      out[j][0] = pack_w(r[0], r[1], r[2], 0);           // window at -1
+    } else if (C == 1 && K == 5) {
+      out[j][0] = pack_w(r[0], r[1], r[2], r[3]);        // window at -2
+      out[j][1] = pack_w(r[4], 0, 0, 0);                 // window at +2
+    } else if (C == 3 && K == 3) {
+      out[j][0] = pack_w(r[0], 0, 0, r[1]);              // window at -3: taps -3, 0
+      out[j][1] = pack_w(0, 0, 0, r[2]);                 // window at  0: tap +3
+    } else {
+      out[j][0] = pack_w(r[0], 0, 0, r[1]);              // window at -6: taps -6, -3
+      out[j][1] = pack_w(r[2], 0, 0, r[3]);              // window at  0: taps 0, +3
+      out[j][2] = pack_w(0, 0, 0, r[4]);                 // window at +3: tap +6
+    }
+  }
+}
+
+}  // namespace
+
+struct b2i_plan {
+  b2i_chain_t chain;
+  int cin = 0, cout = 0, halo = 0;
+  std::vector<Segment> segs;
+  b2i_plan_info_t info;
+};
+
+namespace {
+
+// Builds the tile-kernel phases of one segment from its elements.
+int build_tile_segment(const std::vector<Elem>& el, int cin, Segment& seg) {
+  seg.pointwise = false;
+  seg.cin = cin;
+  seg.phases.clear();
+  seg.n_luts = 0;
+  int c = cin;
+  auto add_lut = [&](PhaseDesc& ph, const uint8_t* lut) -> int {
+    if (ph.lut >= 0) {
+      compose_lut(seg.luts[ph.lut], lut);
+      return B2I_OK;
+    }
+    if (seg.n_luts >= kMaxLuts) return B2I_ERR_UNSUPPORTED;
+    memcpy(seg.luts[seg.n_luts], lut, 256);
+    ph.lut = seg.n_luts++;
+    return B2I_OK;
+  };
+  for (size_t i = 0; i < el.size(); ++i) {
+    const Elem& e = el[i];
+    PhaseDesc ph;
+    memset(&ph, 0, sizeof ph);
+    ph.lut = -1;
+    ph.fix_border = -1;
+    ph.cin = c;
+    switch (e.kind) {
+      case B2I_OP_LUT:
+        if (!seg.phases.empty()) {  // rides on the previous phase's result
+          if (add_lut(seg.phases.back(), e.lut) != B2I_OK) return B2I_ERR_UNSUPPORTED;
+          continue;
+        }
+        ph.type = PH_COPY;
+        ph.cout = c;
+        if (add_lut(ph, e.lut) != B2I_OK) return B2I_ERR_UNSUPPORTED;
+        break;
+      case B2I_OP_GRAY_REF:
+      case B2I_OP_GRAY_CV:
+        ph.type = e.kind == B2I_OP_GRAY_REF ? PH_GRAY_REF : PH_GRAY_CV;
+        ph.cout = c = 1;
+        break;
+      case B2I_OP_EXPAND:
+        if (!seg.phases.empty() &&
+            (seg.phases.back().type == PH_STENCIL || seg.phases.back().type == PH_SOBEL) &&
+            !seg.phases.back().expand) {
+          seg.phases.back().expand = 1;  // kernel.cu:210 fused into the stencil's store
+          seg.phases.back().cout = c = 3;
+          continue;
+        }
+        ph.type = PH_EXPAND;
+        ph.cout = c = 3;
+        break;
+      default: {  // stencil / sobel
+        const b2i_op_t& op = *e.op;
+        ph.type = op.kind == B2I_OP_SOBEL ? PH_SOBEL : PH_STENCIL;
+        ph.cout = c;
+        ph.border = op.border;
+        ph.ksize = op.kind == B2I_OP_SOBEL ? 3 : op.ksize;
+        ph.shift = op.shift;
+        ph.bias = op.bias;
+        int w[25];
+        if (op.kind == B2I_OP_SOBEL) {
+          const int gx[9] = {-1, 0, 1, -2, 0, 2, -1, 0, 1}, gy[9] = {-1, -2, -1, 0, 0, 0, 1, 2, 1};
+          uint32_t tmp[5][3];
+          pack_rows(c, 3, gx, ph.wpk);
+          pack_rows(c, 3, gy, tmp);
+          memcpy(ph.wpk2, tmp, sizeof ph.wpk2);
+        } else {
+          for (int q = 0; q < ph.ksize * ph.ksize; ++q) w[q] = op.weights[q];
+          pack_rows(c, ph.ksize, w, ph.wpk);
+        }
+        break;
+      }
+    }
+    seg.phases.push_back(ph);
+  }
+  if (seg.phases.empty() || (int)seg.phases.size() > kMaxPhases) return B2I_ERR_UNSUPPORTED;
+  seg.cout = c;
+  // margins, walking backwards: a phase must produce what the later stencils still consume
+  int margin = 0;
+  for (int k = (int)seg.phases.size() - 1; k >= 0; --k) {
+    PhaseDesc& ph = seg.phases[k];
+    ph.margin = margin;
+    if (ph.type == PH_STENCIL || ph.type == PH_SOBEL) margin += ph.ksize / 2;
+  }
+  seg.halo = margin;
+  if (seg.halo > kMaxSegHalo) return B2I_ERR_UNSUPPORTED;
+  // buffers: RAW -> A -> B -> A ... -> STAGE
+  seg.chan_a = seg.chan_b = 0;
+  int src = BUF_RAW;
+  for (size_t k = 0; k < seg.phases.size(); ++k) {
+    PhaseDesc& ph = seg.phases[k];
+    ph.src = src;
+    const bool last = k + 1 == seg.phases.size();
+    ph.dst = last ? BUF_STAGE : (src == BUF_A ? BUF_B : BUF_A);
+    if (ph.dst == BUF_A) seg.chan_a = std::max(seg.chan_a, ph.cout);
+    if (ph.dst == BUF_B) seg.chan_b = std::max(seg.chan_b, ph.cout);
+    src = ph.dst;
+    // the border rule a following stencil needs painted onto this phase's result
+    if (!last) {
+      const PhaseDesc& nx = seg.phases[k + 1];
+      if ((nx.type == PH_STENCIL || nx.type == PH_SOBEL) && nx.border != B2I_BORDER_REF)
+        ph.fix_border = nx.border;
+    }
+  }
+  const PhaseDesc& p0 = seg.phases[0];
+  seg.raw_fix_border = -1;
+  if ((p0.type == PH_STENCIL || p0.type == PH_SOBEL) &&
+      (p0.border == B2I_BORDER_REFLECT101 || p0.border == B2I_BORDER_REPLICATE))
+    seg.raw_fix_border = p0.border;  // ZERO is what TMA's out-of-bounds fill already gives
+  return B2I_OK;
+}
+
+// [lut] [gray] [lut] [expand] [lut]: the shapes the streaming kernel takes.
+bool build_pointwise_segment(const std::vector<Elem>& el, int cin, Segment& seg) {
+  seg.pointwise = true;
+  seg.cin = cin;
+  seg.halo = 0;
+  seg.pw_gray = seg.pw_expand = seg.pw_has_lut0 = seg.pw_has_lut1 = 0;
+  int c = cin;
+  for (const Elem& e : el) {
+    switch (e.kind) {
+      case B2I_OP_LUT:
+        if (!seg.pw_gray && !seg.pw_expand) {  // before any channel change: lut0 (or lut1 if no gray follows)
+          if (seg.pw_has_lut0) compose_lut(seg.pw_lut0, e.lut);
+          else memcpy(seg.pw_lut0, e.lut, 256), seg.pw_has_lut0 = 1;
+        } else {  // after gray and/or expand: per byte, commutes with the replication
+          if (seg.pw_has_lut1) compose_lut(seg.pw_lut1, e.lut);
+          else memcpy(seg.pw_lut1, e.lut, 256), seg.pw_has_lut1 = 1;
+        }
+        break;
+      case B2I_OP_GRAY_REF:
+      case B2I_OP_GRAY_CV:
+        if (seg.pw_gray || seg.pw_expand || c != 3) return false;
+        seg.pw_gray = e.kind == B2I_OP_GRAY_REF ? 1 : 2;
+        c = 1;
+        break;
+      case B2I_OP_EXPAND:
+        if (seg.pw_expand || c != 1) return false;
+        seg.pw_expand = 1;
+        c = 3;
+        break;
+      default:
+        return false;
+    }
+  }
+  seg.cout = c;
+  return true;
+}
+
+PFN_cuTensorMapEncodeTiled_v12000 tensor_map_encoder() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+  });
+  return fn;
+}
+
+// 2-D byte image as a tensor of 32-bit elements: dim0 = row_bytes/4, dim1 = rows.
+bool encode_map(CUtensorMap* m, uint64_t ptr, int64_t pitch, int64_t row_bytes, int rows,
+                int box_w_bytes, int box_rows) {
+  auto enc = tensor_map_encoder();
+  if (!enc || rows <= 0) return false;
+  if ((ptr & 15) || (pitch & 15) || (row_bytes & 3) || pitch <= 0) return false;
+  cuuint64_t gdim[2] = {(cuuint64_t)(row_bytes / 4), (cuuint64_t)rows};
+  cuuint64_t gstr[1] = {(cuuint64_t)pitch};
+  cuuint32_t box[2] = {(cuuint32_t)(box_w_bytes / 4), (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  if (box[0] > 256 || box[1] > 256) return false;
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, reinterpret_cast<void*>(ptr), gdim, gstr, box,
+             estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+int align_up(int v, int a) { return (v + a - 1) / a * a; }
+
+// Shared-memory layout of a tile segment for tile height th. Every buffer starts 128-byte
+// aligned behind a 128-byte gap: stencil threads read 8 bytes to the left of a strip.
+void layout(const Segment& seg, int th, TileParams& P) {
+  const int R = seg.halo, rows_alloc = th + 2 * R + kRowGroup;
+  int off = 0;
+  auto place = [&](int bytes) {
+    off = align_up(off, 128) + 128;
+    const int o = off;
+    off += bytes;
+    return o;
+  };
+  P.th = th;
+  P.halo = R;
+  P.raw_rows = th + 2 * R;
+  const int raw_pitch = kPlaneW * seg.cin;
+  P.raw_tx_bytes = raw_pitch * P.raw_rows;
+  P.raw_stage_bytes = align_up(raw_pitch * rows_alloc, 128) + 128;
+  P.buf[BUF_RAW] = {place(2 * P.raw_stage_bytes), raw_pitch, 0, 0};
+  P.buf[BUF_A] = {seg.chan_a ? place(kPlaneW * seg.chan_a * rows_alloc) : 0, kPlaneW * seg.chan_a, 0, 0};
+  P.buf[BUF_B] = {seg.chan_b ? place(kPlaneW * seg.chan_b * rows_alloc) : 0, kPlaneW * seg.chan_b, 0, 0};
+  P.buf[BUF_STAGE] = {place(kTileW * seg.cout * th), kTileW * seg.cout, kApron, R};
+  P.lut_off = place(kMaxLuts * 256);
+  P.bar_off = place(64);
+  P.smem_bytes = align_up(off, 128);
+}
+
+struct DeviceInfo {
+  int sms = 0;
+  int bps_for_smem[2] = {0, 0};  // cache key: smem bytes -> blocks/SM
+  int bps = 0;
+};
+
+int device_sms(int dev, int* sms) {
+  static int cache[64] = {0};
+  if (dev >= 0 && dev < 64 && cache[dev]) {
+    *sms = cache[dev];
+    return B2I_OK;
+  }
+  B2I_CUDA(cudaDeviceGetAttribute(sms, cudaDevAttrMultiProcessorCount, dev));
+  if (dev >= 0 && dev < 64) cache[dev] = *sms;
+  return B2I_OK;
+}
+
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v && *v ? atoi(v) : dflt;
+}
+
+// One tile-kernel launch: rows [y0,y1) of this segment's result.
+int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
+                        const b2i_view_t& src, const b2i_view_t& dst, bool first, bool last) {
+  int dev = 0, sms = 0;
+  B2I_CUDA(cudaGetDevice(&dev));
+  B2I_TRY(device_sms(dev, &sms));
+  TileParams P;
+  memset(&P, 0, sizeof P);
+  // tile height: tallest that still lets two CTAs share an SM; smaller for small images so that
+  // every SM gets tiles
+  int th = L.tile_h > 0 ? L.tile_h : env_int("B200IMG_TILE_H", 0);
+  const int tiles_x = (L.W + kTileW - 1) / kTileW;
+  if (th <= 0) {
+    const int cands[4] = {32, 24, 16, 8};
+    th = 8;
+    for (int c : cands) {
+      layout(seg, c, P);
+      if (P.smem_bytes <= 113 * 1024) {
+        th = c;
+        break;
+      }
+    }
+    while (th > 8 && tiles_x * ((y1 - y0 + th - 1) / th) < 2 * sms) th -= 8;
+  }
+  B2I_CHECK_ARG(th >= 4 && th <= kMaxTileH, "tile height %d out of range", th);
+  layout(seg, th, P);
+  if (P.smem_bytes > 227 * 1024)
+    B2I_FAIL(B2I_ERR_UNSUPPORTED, "segment needs %d bytes of shared memory", P.smem_bytes);
+  P.W = L.W;
+  P.H = L.H;
+  P.cin = seg.cin;
+  P.cout = seg.cout;
+  P.y0 = y0;
+  P.y1 = y1;
+  P.tiles_x = tiles_x;
+  P.tiles_y = (y1 - y0 + th - 1) / th;
+  P.n_tiles = P.tiles_x * P.tiles_y;
+  P.n_phases = (int)seg.phases.size();
+  P.rgb_order = plan->chain.order == B2I_ORDER_RGB;
+  P.raw_fix_border = seg.raw_fix_border;
+  for (int k = 0; k < P.n_phases; ++k) P.ph[k] = seg.phases[k];
+  memcpy(P.luts, seg.luts, sizeof P.luts);
+  // views
+  B2I_CHECK_ARG(src.ptr && dst.ptr, "null image view");
+  const int need_a = std::max(0, y0 - seg.halo), need_b = std::min(L.H, y1 + seg.halo);
+  B2I_CHECK_ARG(src.y_begin <= need_a && src.y_end >= need_b,
+                "source view rows [%d,%d) do not cover the rows [%d,%d) this band reads",
+                src.y_begin, src.y_end, need_a, need_b);
+  B2I_CHECK_ARG(dst.y_begin <= y0 && dst.y_end >= y1, "destination view rows [%d,%d) do not "
+                "cover the band [%d,%d)", dst.y_begin, dst.y_end, y0, y1);
+  P.src_ptr = src.ptr;
+  P.src_pitch = src.pitch;
+  P.src_y_begin = src.y_begin;
+  P.src_y_end = std::min(src.y_end, L.H);
+  P.dst_ptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
+  P.dst_pitch = dst.pitch;
+  P.dst_y_begin = y0;
+  P.dst_y_end = y1;
+  const bool no_tma = (L.flags & B2I_LAUNCH_NO_TMA) || env_int("B200IMG_NO_TMA", 0);
+  CUtensorMap src_map, dst_map, up_map, dn_map;
+  memset(&src_map, 0, sizeof src_map);
+  memset(&dst_map, 0, sizeof dst_map);
+  memset(&up_map, 0, sizeof up_map);
+  memset(&dn_map, 0, sizeof dn_map);
+  P.use_tma_load = !no_tma && encode_map(&src_map, P.src_ptr, P.src_pitch, (int64_t)L.W * seg.cin,
+                                         P.src_y_end - P.src_y_begin, kPlaneW * seg.cin, P.raw_rows);
+  P.use_tma_store = !no_tma && encode_map(&dst_map, P.dst_ptr, P.dst_pitch, (int64_t)L.W * seg.cout,
+                                          y1 - y0, kTileW * seg.cout, th);
+  // multi-GPU hooks: waits guard the first segment's ghost-row reads, pushes and signals ride
+  // on the last segment's stores
+  if (first) {
+    P.wait_up_flag = L.wait_up_flag;
+    P.wait_dn_flag = L.wait_dn_flag;
+    P.wait_epoch = L.wait_epoch;
+  }
+  if (last) {
+    P.signal_up_flag = L.signal_up_flag;
+    P.signal_dn_flag = L.signal_dn_flag;
+    P.done_flag = L.done_flag;
+    P.signal_epoch = L.signal_epoch;
+    if (L.push_rows > 0 && (L.push_up.ptr || L.push_dn.ptr)) {
+      B2I_CHECK_ARG(L.push_rows <= y1 - y0 && L.push_rows <= kGhostRows,
+                    "push_rows %d exceeds the band height or the %d ghost rows", L.push_rows,
+                    kGhostRows);
+      P.push_rows = L.push_rows;
+      P.push_pitch = L.push_up.ptr ? L.push_up.pitch : L.push_dn.pitch;
+      B2I_CHECK_ARG(!(L.push_up.ptr && L.push_dn.ptr) || L.push_up.pitch == L.push_dn.pitch,
+                    "push views must share one pitch");
+      if (L.push_up.ptr) {  // view: rows [y0, y0+push_rows) of the result, ptr at row y_begin
+        B2I_CHECK_ARG(L.push_up.y_begin <= y0 && L.push_up.y_end >= y0 + L.push_rows,
+                      "push_up view does not cover rows [%d,%d)", y0, y0 + L.push_rows);
+        P.push_up_ptr = L.push_up.ptr + (uint64_t)((int64_t)(y0 - L.push_up.y_begin) * L.push_up.pitch);
+        P.push_up_y_begin = y0;
+      }
+      if (L.push_dn.ptr) {
+        const int a = y1 - L.push_rows;
+        B2I_CHECK_ARG(L.push_dn.y_begin <= a && L.push_dn.y_end >= y1,
+                      "push_dn view does not cover rows [%d,%d)", a, y1);
+        P.push_dn_ptr = L.push_dn.ptr + (uint64_t)((int64_t)(a - L.push_dn.y_begin) * L.push_dn.pitch);
+        P.push_dn_y_begin = a;
+      }
+      if (P.use_tma_store) {
+        bool ok = true;
+        if (P.push_up_ptr)
+          ok = ok && encode_map(&up_map, P.push_up_ptr, P.push_pitch, (int64_t)L.W * seg.cout,
+                                P.push_rows, kTileW * seg.cout, th);
+        if (P.push_dn_ptr)
+          ok = ok && encode_map(&dn_map, P.push_dn_ptr, P.push_pitch, (int64_t)L.W * seg.cout,
+                                P.push_rows, kTileW * seg.cout, th);
+        if (!ok) {  // fall back to plain stores for everything
+          P.use_tma_store = 0;
+        }
+      }
+    }
+  }
+  if (P.wait_up_flag || P.wait_dn_flag || P.signal_up_flag || P.signal_dn_flag || P.done_flag) {
+    B2I_CHECK_ARG(L.counters && L.status, "flag use needs the counters and status scratch words");
+    P.counters = L.counters;
+    P.status = L.status;
+  }
+  P.timeout_ns = L.timeout_ns ? L.timeout_ns : 2000000000ull;
+  // persistent grid: resident CTAs per SM x SMs, never more than there are tiles
+  static std::mutex mu;
+  static int occ_cache_smem[8] = {0}, occ_cache_bps[8] = {0};
+  int bps = 0;
+  {
+    std::lock_guard<std::mutex> g(mu);
+    for (int i = 0; i < 8; ++i)
+      if (occ_cache_smem[i] == P.smem_bytes + dev * (1 << 20)) bps = occ_cache_bps[i];
+    if (!bps) {
+      B2I_CUDA(tile_chain_occupancy(P.smem_bytes, &bps));
+      static int next = 0;
+      occ_cache_smem[next & 7] = P.smem_bytes + dev * (1 << 20);
+      occ_cache_bps[next & 7] = bps;
+      ++next;
+    }
+  }
+  if (bps < 1) B2I_FAIL(B2I_ERR_UNSUPPORTED, "tile kernel does not fit on an SM (%d B smem)", P.smem_bytes);
+  const int grid = std::max(1, std::min(P.n_tiles, sms * bps));
+  plan->info.last_tile_h = th;
+  plan->info.last_smem_bytes = P.smem_bytes;
+  plan->info.last_grid = grid;
+  plan->info.last_blocks_per_sm = bps;
+  plan->info.last_tma_load = P.use_tma_load;
+  plan->info.last_tma_store = P.use_tma_store;
+  plan->info.last_launches++;
+  B2I_CUDA(launch_tile_chain(P, src_map, dst_map, up_map, dn_map, grid, (cudaStream_t)L.stream));
+  return B2I_OK;
+}
+
+int launch_pointwise_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
+                             int y1, const b2i_view_t& src, const b2i_view_t& dst, bool last) {
+  int dev = 0, sms = 0;
+  B2I_CUDA(cudaGetDevice(&dev));
+  B2I_TRY(device_sms(dev, &sms));
+  B2I_CHECK_ARG(src.ptr && dst.ptr, "null image view");
+  B2I_CHECK_ARG(src.y_begin <= y0 && src.y_end >= y1 && dst.y_begin <= y0 && dst.y_end >= y1,
+                "views do not cover the band [%d,%d)", y0, y1);
+  PointwiseParams P;
+  memset(&P, 0, sizeof P);
+  P.W = L.W;
+  P.cin = seg.cin;
+  P.cout = seg.cout;
+  P.rows = y1 - y0;
+  P.gray = seg.pw_gray;
+  P.expand = seg.pw_expand;
+  P.rgb_order = plan->chain.order == B2I_ORDER_RGB;
+  P.has_lut0 = seg.pw_has_lut0;
+  P.has_lut1 = seg.pw_has_lut1;
+  memcpy(P.lut0, seg.pw_lut0, 256);
+  memcpy(P.lut1, seg.pw_lut1, 256);
+  P.src_pitch = src.pitch;
+  P.dst_pitch = dst.pitch;
+  P.src_ptr = src.ptr + (uint64_t)((int64_t)(y0 - src.y_begin) * src.pitch);
+  P.dst_ptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
+  P.vec_ok = !((P.src_ptr | P.dst_ptr | (uint64_t)P.src_pitch | (uint64_t)P.dst_pitch) & 15) &&
+             !env_int("B200IMG_NO_VEC", 0);
+  if (last && L.done_flag) {
+    B2I_CHECK_ARG(L.counters, "done_flag needs the counters scratch words");
+    P.done_flag = L.done_flag;
+    P.counters = L.counters;
+    P.signal_epoch = L.signal_epoch;
+  }
+  const long long units = (long long)((L.W + 15) / 16) * P.rows;
+  const long long want = (units + 255) / 256;
+  const int grid = (int)std::max(1LL, std::min(want, (long long)sms * 8));
+  plan->info.last_grid = grid;
+  plan->info.last_tile_h = 0;
+  plan->info.last_smem_bytes = 512;
+  plan->info.last_tma_load = plan->info.last_tma_store = 0;
+  plan->info.last_launches++;
+  B2I_CUDA(launch_pointwise(P, grid, (cudaStream_t)L.stream));
+  return B2I_OK;
+}
+
+}  // namespace
+
+extern "C" int b2i_plan_create(const b2i_chain_t* chain, int in_channels, b2i_plan_t** out) {
+  B2I_CHECK_ARG(chain && out, "null argument");
+  const int cout = b2i_chain_out_channels(chain, in_channels);
+  if (cout < 0) return cout;
+  b2i_plan* plan = new b2i_plan();
+  plan->chain = *chain;
+  plan->cin = in_channels;
+  plan->cout = cout;
+  plan->halo = b2i_chain_halo(chain);
+  memset(&plan->info, 0, sizeof plan->info);
+  // fold runs of LUTs
+  std::vector<Elem> el;
+  for (int i = 0; i < chain->n_ops; ++i) {
+    const b2i_op_t& op = chain->ops[i];
+    if (op.kind == B2I_OP_LUT && !el.empty() && el.back().kind == B2I_OP_LUT) {
+      compose_lut(el.back().lut, op.lut);
+      continue;
+    }
+    Elem e;
+    e.kind = op.kind;
+    e.op = &plan->chain.ops[i];
+    if (op.kind == B2I_OP_LUT) memcpy(e.lut, op.lut, 256);
+    el.push_back(e);
+  }
+  // greedy segmentation: extend the segment while the tile kernel can still absorb it
+  size_t i = 0;
+  int c = in_channels;
+  while (i < el.size()) {
+    Segment best;
+    size_t best_end = i;
+    bool have = false;
+    for (size_t end = i + 1; end <= el.size(); ++end) {
+      std::vector<Elem> sub(el.begin() + i, el.begin() + end);
+      bool stencil = false;
+      for (const Elem& e : sub) stencil = stencil || e.kind == B2I_OP_STENCIL || e.kind == B2I_OP_SOBEL;
+      Segment seg;
+      bool ok = false;
+      if (!stencil) ok = build_pointwise_segment(sub, c, seg);
+      if (!ok) ok = build_tile_segment(sub, c, seg) == B2I_OK;
+      if (ok) {
+        TileParams P;  // also has to fit in shared memory at the smallest tile height
+        if (!seg.pointwise) {
+          layout(seg, 8, P);
+          ok = P.smem_bytes <= 227 * 1024;
+        }
+      }
+      if (!ok) break;
+      best = seg;
+      best_end = end;
+      have = true;
+    }
+    if (!have) {
+      delete plan;
+      B2I_FAIL(B2I_ERR_UNSUPPORTED, "op %zu of the chain cannot be scheduled on the GPU", i);
+    }
+    c = best.cout;
+    plan->segs.push_back(best);
+    i = best_end;
+  }
+  plan->info.cin = in_channels;
+  plan->info.cout = cout;
+  plan->info.halo = plan->halo;
+  plan->info.n_segments = (int)plan->segs.size();
+  for (size_t s = 0; s < plan->segs.size() && s < B2I_MAX_OPS; ++s) {
+    plan->info.seg_pointwise[s] = plan->segs[s].pointwise;
+    plan->info.seg_halo[s] = plan->segs[s].halo;
+    plan->info.seg_phases[s] = (int)plan->segs[s].phases.size();
+    plan->info.seg_cout[s] = plan->segs[s].cout;
+  }
+  *out = plan;
+  return B2I_OK;
+}
+
+extern "C" void b2i_plan_destroy(b2i_plan_t* plan) { delete plan; }
+extern "C" int b2i_plan_halo(const b2i_plan_t* plan) { return plan ? plan->halo : 0; }
+extern "C" int b2i_plan_info(const b2i_plan_t* plan, b2i_plan_info_t* info) {
+  B2I_CHECK_ARG(plan && info, "null argument");
+  *info = plan->info;
+  return B2I_OK;
+}
+
+extern "C" int b2i_cuda_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+extern "C" int b2i_cuda_run(b2i_plan_t* plan, const b2i_launch_t* Lp) {
+  B2I_CHECK_ARG(plan && Lp, "null argument");
+  const b2i_launch_t& L = *Lp;
+  B2I_CHECK_ARG(L.W > 0 && L.H > 0 && 0 <= L.y0 && L.y0 <= L.y1 && L.y1 <= L.H,
+                "bad geometry %dx%d rows [%d,%d)", L.W, L.H, L.y0, L.y1);
+  if (L.y0 == L.y1) return B2I_OK;
+  plan->info.last_launches = 0;
+  const int n = (int)plan->segs.size();
+  // Degenerate images (narrower or shorter than a border fold can reach) and explicit requests
+  // go to the reference-style kernels.
+  const bool tiny = plan->halo > 0 && (L.W <= 2 * kApron || L.H <= 2 * kApron);
+  if ((L.flags & B2I_LAUNCH_NAIVE) || tiny) {
+    B2I_CHECK_ARG(L.y0 == 0 && L.y1 == L.H, "the reference-style path runs whole images only");
+    B2I_CHECK_ARG(L.tmp[0].ptr && L.tmp[1].ptr, "the reference-style path needs both tmp images");
+    B2I_CHECK_ARG(L.src.y_begin == 0 && L.dst.y_begin == 0 && L.src.y_end >= L.H && L.dst.y_end >= L.H,
+                  "the reference-style path needs whole-image views");
+    // LUT scratch: the tail of tmp[1] beyond its W*H*3 image bytes is not guaranteed, so LUTs
+    // live in the first tmp row of a third region the caller passes through `status`
+    B2I_CHECK_ARG(L.counters, "the reference-style path needs 256*B2I_MAX_OPS bytes at `counters`");
+    return run_naive(&plan->chain, reinterpret_cast<const uint8_t*>(L.src.ptr), L.W, L.H, plan->cin,
+                     (size_t)L.src.pitch, reinterpret_cast<uint8_t*>(L.dst.ptr), (size_t)L.dst.pitch,
+                     reinterpret_cast<uint8_t*>(L.tmp[0].ptr), reinterpret_cast<uint8_t*>(L.tmp[1].ptr),
+                     reinterpret_cast<uint8_t*>(L.counters), (cudaStream_t)L.stream);
+  }
+  // Multi-segment plans over-compute: segment s produces the rows later segments still read
+  // (communication-avoiding), so no synchronisation is needed inside one call.
+  std::vector<int> rem(n + 1, 0);
+  for (int s = n - 1; s >= 0; --s) rem[s] = rem[s + 1] + plan->segs[s].halo;
+  b2i_view_t cur = L.src;
+  for (int s = 0; s < n; ++s) {
+    const Segment& seg = plan->segs[s];
+    const bool last = s == n - 1;
+    const int ya = last ? L.y0 : std::max(0, L.y0 - rem[s + 1]);
+    const int yb = last ? L.y1 : std::min(L.H, L.y1 + rem[s + 1]);
+    b2i_view_t out = L.dst;
+    if (!last) {
+      out = L.tmp[s & 1];
+      B2I_CHECK_ARG(out.ptr, "plan has %d segments: tmp[%d] is needed", n, s & 1);
+      B2I_CHECK_ARG(out.pitch >= (int64_t)L.W * seg.cout, "tmp pitch too small");
+    }
+    if (seg.pointwise) B2I_TRY(launch_pointwise_segment(plan, seg, L, ya, yb, cur, out, last));
+    else B2I_TRY(launch_tile_segment(plan, seg, L, ya, yb, cur, out, s == 0, last));
+    cur = out;
+    if (!last) {  // later segments may read exactly what this one produced
+      cur.ptr = out.ptr + (uint64_t)((int64_t)(ya - out.y_begin) * out.pitch);
+      cur.y_begin = ya;
+      cur.y_end = yb;
+    }
+  }
+  return B2I_OK;
+}
+
+extern "C" int b2i_cuda_run_image(b2i_plan_t* plan, uint64_t src, int64_t src_pitch, uint64_t dst,
+                                  int64_t dst_pitch, int W, int H, uint64_t tmp0, uint64_t tmp1,
+                                  uint64_t lut_scratch, void* stream, int flags) {
+  B2I_CHECK_ARG(plan, "null plan");
+  b2i_launch_t L;
+  memset(&L, 0, sizeof L);
+  L.W = W;
+  L.H = H;
+  L.y0 = 0;
+  L.y1 = H;
+  L.src = {src, src_pitch, 0, H};
+  L.dst = {dst, dst_pitch, 0, H};
+  L.tmp[0] = {tmp0, (int64_t)W * 3, 0, H};
+  L.tmp[1] = {tmp1, (int64_t)W * 3, 0, H};
+  L.counters = lut_scratch;
+  L.stream = stream;
+  L.flags = flags;
+  return b2i_cuda_run(plan, &L);
+}

@@ -143,6 +143,112 @@ void b2i_free(void* p);
 /* Deterministic synthetic test card (gradients + edges + hashed noise), any size. */
 int b2i_synth_image(uint8_t* dst, int W, int H, int C, size_t pitch, uint32_t seed);
 
+/* ---- CUDA path: plans and band launches (csrc/runtime/plan.cpp, csrc/kernels) ------------- */
+
+/* A plan is a chain compiled for a given input channel count: LUTs folded, ops grouped into
+ * segments (one kernel launch each), every stencil lowered to packed dp4a weights. */
+typedef struct b2i_plan b2i_plan_t;
+
+/* Rows [y_begin, y_end) of an image, addressable from the device that launches: local memory,
+ * a peer GPU's memory (cudaDeviceEnablePeerAccess) or an IPC mapping. ptr is row y_begin. */
+typedef struct b2i_view {
+  uint64_t ptr;
+  int64_t pitch;
+  int32_t y_begin, y_end;
+} b2i_view_t;
+
+#define B2I_LAUNCH_NO_TMA 1   /* force the plain ld/st tile loaders (debug, unaligned images) */
+#define B2I_LAUNCH_NAIVE 2    /* reference-style one-launch-per-op kernels (baseline / oracle) */
+
+/* One band launch: produce rows [y0, y1) of chain(image) into dst, reading src.
+ * src must cover rows [y0-halo, y1+halo) clipped to the image (halo = b2i_plan_halo); when src
+ * is another GPU's image this IS the scatter, when dst is the root GPU's image this IS the
+ * gather. Nothing is allocated and nothing synchronises with the host. */
+typedef struct b2i_launch {
+  int32_t W, H;          /* whole-image geometry */
+  int32_t y0, y1;        /* rows to produce */
+  b2i_view_t src, dst;
+  b2i_view_t tmp[2];     /* scratch images for plans with more than one segment (3 bytes/pixel,
+                            rows [y0-halo, y1+halo) clipped); ptr 0 when the plan has one segment */
+  /* multi-GPU hooks, all optional (0) */
+  b2i_view_t push_up, push_dn; /* neighbours' ghost rows: rows [y0,y0+push_rows) resp.
+                                  [y1-push_rows,y1) of the result are stored there as well */
+  int32_t push_rows;
+  uint32_t wait_epoch, signal_epoch;
+  uint64_t wait_up_flag, wait_dn_flag;     /* u32 flags in local memory */
+  uint64_t signal_up_flag, signal_dn_flag; /* u32 flags in the neighbours' memory */
+  uint64_t done_flag;                      /* u32 flag (root GPU): set when every row is stored */
+  uint64_t counters;                       /* 16 zeroed bytes of local device memory */
+  uint64_t status;                         /* u32 in local device memory, nonzero = wait timed out */
+  uint64_t timeout_ns;                     /* 0 = 2 s */
+  void* stream;                            /* cudaStream_t */
+  int32_t tile_h;                          /* 0 = choose */
+  int32_t flags;                           /* B2I_LAUNCH_* */
+} b2i_launch_t;
+
+typedef struct b2i_plan_info {
+  int32_t cin, cout, halo, n_segments;
+  int32_t seg_pointwise[B2I_MAX_OPS], seg_halo[B2I_MAX_OPS], seg_phases[B2I_MAX_OPS];
+  int32_t seg_cout[B2I_MAX_OPS];
+  /* filled by the last b2i_cuda_run on this plan (not thread-safe, for reports) */
+  int32_t last_tile_h, last_smem_bytes, last_grid, last_blocks_per_sm, last_tma_load,
+      last_tma_store, last_launches;
+} b2i_plan_info_t;
+
+int b2i_plan_create(const b2i_chain_t* chain, int in_channels, b2i_plan_t** out);
+void b2i_plan_destroy(b2i_plan_t* plan);
+int b2i_plan_halo(const b2i_plan_t* plan);
+int b2i_plan_info(const b2i_plan_t* plan, b2i_plan_info_t* info);
+int b2i_cuda_run(b2i_plan_t* plan, const b2i_launch_t* launch);
+/* Whole image, device pointers, current device, no bands: the call the torch front end makes.
+ * tmp0/tmp1: W*H*3 bytes each, needed for multi-segment plans and B2I_LAUNCH_NAIVE (with
+ * lut_scratch: 256*B2I_MAX_OPS bytes); may be 0 otherwise. */
+int b2i_cuda_run_image(b2i_plan_t* plan, uint64_t src, int64_t src_pitch, uint64_t dst,
+                       int64_t dst_pitch, int W, int H, uint64_t tmp0, uint64_t tmp1,
+                       uint64_t lut_scratch, void* stream, int flags);
+int b2i_cuda_device_count(void);
+/* Host image in, host image out on one GPU: upload, `iters` runs (one warm-up first when
+ * iters > 1), download. kernel_ms is the device-event time of one run, total_ms the wall time
+ * of the whole call. The reference's kernel.cu:147-206 sequence in one call. */
+int b2i_cuda_run_host_image(const b2i_chain_t* chain, const uint8_t* src, int W, int H, int C,
+                            size_t src_pitch, uint8_t* dst, size_t dst_pitch, int device,
+                            int iters, int flags, double* kernel_ms, double* total_ms);
+
+/* ---- multi-GPU runtime (csrc/runtime/context.cpp): what stands where the reference has MPI -- */
+
+/* JSON report: devices (name, SMs, memory, NVLS multicast support) and the P2P matrix
+ * (access, native atomics, performance rank). MPI_Comm_size/rank become this discovery. */
+int b2i_topology_json(char* buf, size_t len);
+
+typedef struct b2i_ctx b2i_ctx_t;
+/* One process drives n_gpus devices (devices == NULL: 0..n-1, wrapping onto the devices that
+ * exist, so multi-band runs can be tested on one GPU). Peer access is enabled all-to-all. */
+int b2i_ctx_create(int n_gpus, const int* devices, int root, b2i_ctx_t** out);
+void b2i_ctx_destroy(b2i_ctx_t* ctx);
+int b2i_ctx_gpus(const b2i_ctx_t* ctx);
+/* Host image -> the root GPU's source image (kernel.cu:110,163). */
+int b2i_ctx_load_root(b2i_ctx_t* ctx, const uint8_t* src, int W, int H, int C, size_t pitch,
+                      int out_channels);
+/* Root GPU's output image -> host (kernel.cu:202,223). Synchronises. */
+int b2i_ctx_fetch_root(b2i_ctx_t* ctx, uint8_t* dst, size_t pitch);
+/* ROOT mode: scatter and gather fused into the filter kernels (peer loads from / peer stores
+ * to the root GPU). kernel_ms: slowest GPU, device events, per iteration. */
+int b2i_ctx_run_root(b2i_ctx_t* ctx, b2i_plan_t* plan, int iters, int flags, double* kernel_ms,
+                     double* per_gpu_ms);
+/* RESIDENT mode: bands stay on their GPUs for `passes` applications of the chain; halos are
+ * pushed into the neighbours' ghost rows by the filter kernel itself. use_flags: device-side
+ * release/acquire flags instead of cross-device stream events between passes. */
+int b2i_ctx_run_resident(b2i_ctx_t* ctx, b2i_plan_t* plan, int passes, int flags, int use_flags,
+                         double* kernel_ms, double* per_gpu_ms);
+/* DIRECT mode: host image in, host image out; every GPU moves its own band over its own PCIe
+ * link (pin src/dst for asynchronous copies). */
+int b2i_ctx_run_direct(b2i_ctx_t* ctx, b2i_plan_t* plan, const uint8_t* src, int W, int H, int C,
+                       size_t src_pitch, uint8_t* dst, size_t dst_pitch, int flags,
+                       double* total_ms);
+int b2i_ctx_run_cli(int gpus, int root, const b2i_chain_t* chain, const uint8_t* src, int W, int H,
+                    int C, uint8_t* dst, int iters, int flags, int resident, double* kernel_ms,
+                    double* total_ms, char* report, size_t report_len);
+
 #ifdef __cplusplus
 }
 #endif

@@ -111,3 +111,63 @@ _sig("b2i_synth_image", C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c
 
 def has(symbol: str) -> bool:
     return hasattr(lib, symbol)
+
+
+# ---- CUDA path (present once the kernels are linked in) ----------------------------------------
+LAUNCH_NO_TMA, LAUNCH_NAIVE = 1, 2
+
+
+class View(C.Structure):
+    _fields_ = [("ptr", C.c_uint64), ("pitch", C.c_int64), ("y_begin", C.c_int32),
+                ("y_end", C.c_int32)]
+
+
+class Launch(C.Structure):
+    _fields_ = [
+        ("W", C.c_int32), ("H", C.c_int32), ("y0", C.c_int32), ("y1", C.c_int32),
+        ("src", View), ("dst", View), ("tmp", View * 2),
+        ("push_up", View), ("push_dn", View), ("push_rows", C.c_int32),
+        ("wait_epoch", C.c_uint32), ("signal_epoch", C.c_uint32),
+        ("wait_up_flag", C.c_uint64), ("wait_dn_flag", C.c_uint64),
+        ("signal_up_flag", C.c_uint64), ("signal_dn_flag", C.c_uint64),
+        ("done_flag", C.c_uint64), ("counters", C.c_uint64), ("status", C.c_uint64),
+        ("timeout_ns", C.c_uint64), ("stream", C.c_void_p),
+        ("tile_h", C.c_int32), ("flags", C.c_int32),
+    ]
+
+
+class PlanInfo(C.Structure):
+    _fields_ = [
+        ("cin", C.c_int32), ("cout", C.c_int32), ("halo", C.c_int32), ("n_segments", C.c_int32),
+        ("seg_pointwise", C.c_int32 * B2I_MAX_OPS), ("seg_halo", C.c_int32 * B2I_MAX_OPS),
+        ("seg_phases", C.c_int32 * B2I_MAX_OPS), ("seg_cout", C.c_int32 * B2I_MAX_OPS),
+        ("last_tile_h", C.c_int32), ("last_smem_bytes", C.c_int32), ("last_grid", C.c_int32),
+        ("last_blocks_per_sm", C.c_int32), ("last_tma_load", C.c_int32),
+        ("last_tma_store", C.c_int32), ("last_launches", C.c_int32),
+    ]
+
+
+_sig("b2i_plan_create", C.c_int, _P(ChainStruct), C.c_int, _P(C.c_void_p))
+_sig("b2i_plan_destroy", None, C.c_void_p)
+_sig("b2i_plan_halo", C.c_int, C.c_void_p)
+_sig("b2i_plan_info", C.c_int, C.c_void_p, _P(PlanInfo))
+_sig("b2i_cuda_run", C.c_int, C.c_void_p, _P(Launch))
+_sig("b2i_cuda_run_image", C.c_int, C.c_void_p, C.c_uint64, C.c_int64, C.c_uint64, C.c_int64,
+     C.c_int, C.c_int, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_int)
+_sig("b2i_cuda_device_count", C.c_int)
+
+# ---- multi-GPU runtime ---------------------------------------------------------------------------
+_sig("b2i_topology_json", C.c_int, C.c_char_p, C.c_size_t)
+_sig("b2i_ctx_create", C.c_int, C.c_int, _P(C.c_int), C.c_int, _P(C.c_void_p))
+_sig("b2i_ctx_destroy", None, C.c_void_p)
+_sig("b2i_ctx_gpus", C.c_int, C.c_void_p)
+_sig("b2i_ctx_load_root", C.c_int, C.c_void_p, u8p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_int)
+_sig("b2i_ctx_fetch_root", C.c_int, C.c_void_p, u8p, C.c_size_t)
+_sig("b2i_ctx_run_root", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, _P(C.c_double),
+     _P(C.c_double))
+_sig("b2i_ctx_run_resident", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+     _P(C.c_double), _P(C.c_double))
+_sig("b2i_ctx_run_direct", C.c_int, C.c_void_p, C.c_void_p, u8p, C.c_int, C.c_int, C.c_int,
+     C.c_size_t, u8p, C.c_size_t, C.c_int, _P(C.c_double))
+_sig("b2i_cuda_run_host_image", C.c_int, _P(ChainStruct), u8p, C.c_int, C.c_int, C.c_int,
+     C.c_size_t, u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, _P(C.c_double), _P(C.c_double))

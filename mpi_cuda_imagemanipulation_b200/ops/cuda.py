@@ -1,0 +1,119 @@
+"""Single-GPU CUDA execution of a filter chain on torch tensors (zero-copy, current stream).
+
+The tensor is handed to the sm_100a kernels by address (``data_ptr``); nothing is copied or
+re-laid-out. This is the replacement for the reference's ``cudaMalloc`` / synchronous
+``cudaMemcpy`` / three launches / ``cudaDeviceSynchronize`` / D2H / host ``cvtColor`` sequence
+(``kernel.cu:147-210``): one (or, for long chains, a few) launches on the caller's stream.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from .. import _lib
+from .._lib import Launch, PlanInfo, View, check, lib
+from .chain import Chain, as_chain, image_geometry
+
+
+class Plan:
+    """A chain compiled for ``in_channels`` input (wraps ``b2i_plan_t``)."""
+
+    def __init__(self, chain, in_channels: int, **kw):
+        self.chain: Chain = as_chain(chain, **kw)
+        self.cin = in_channels
+        self._p = C.c_void_p()
+        check(lib.b2i_plan_create(self.chain.ref, in_channels, C.byref(self._p)))
+        self.cout = self.chain.out_channels(in_channels)
+        self._tmp = {}
+
+    def __del__(self):
+        p, self._p = getattr(self, "_p", None), None
+        if p and lib is not None:  # module globals are gone at interpreter shutdown
+            lib.b2i_plan_destroy(p)
+
+    @property
+    def handle(self):
+        return self._p
+
+    @property
+    def halo(self) -> int:
+        return lib.b2i_plan_halo(self._p)
+
+    def info(self) -> dict:
+        pi = PlanInfo()
+        check(lib.b2i_plan_info(self._p, C.byref(pi)))
+        n = pi.n_segments
+        return {
+            "cin": pi.cin, "cout": pi.cout, "halo": pi.halo, "n_segments": n,
+            "segments": [{"pointwise": bool(pi.seg_pointwise[i]), "halo": pi.seg_halo[i],
+                          "phases": pi.seg_phases[i], "cout": pi.seg_cout[i]} for i in range(n)],
+            "tile_h": pi.last_tile_h, "smem_bytes": pi.last_smem_bytes, "grid": pi.last_grid,
+            "blocks_per_sm": pi.last_blocks_per_sm, "tma_load": bool(pi.last_tma_load),
+            "tma_store": bool(pi.last_tma_store), "launches": pi.last_launches,
+        }
+
+    @property
+    def n_segments(self) -> int:
+        return self.info()["n_segments"]
+
+    # scratch images for multi-segment plans / the reference-style path, cached per geometry
+    def scratch(self, device, W: int, H: int):
+        key = (str(device), W, H)
+        if key not in self._tmp:
+            self._tmp[key] = (torch.empty(H * W * 3, dtype=torch.uint8, device=device),
+                              torch.empty(H * W * 3, dtype=torch.uint8, device=device),
+                              torch.zeros(256 * _lib.B2I_MAX_OPS, dtype=torch.uint8, device=device))
+        return self._tmp[key]
+
+    def run(self, src: torch.Tensor, out: Optional[torch.Tensor] = None, *, naive: bool = False,
+            no_tma: bool = False, tile_h: int = 0) -> torch.Tensor:
+        """dst = chain(src) for a whole HxWxC uint8 CUDA tensor on the current stream."""
+        if not src.is_cuda or src.dtype != torch.uint8:
+            raise TypeError("expected a uint8 CUDA tensor")
+        H, W, Cn = image_geometry(src)
+        if Cn != self.cin:
+            raise ValueError(f"plan was built for {self.cin} channels, image has {Cn}")
+        if src.stride(-1) != 1 and src.ndim == 3 or (src.ndim == 3 and src.stride(1) != Cn):
+            src = src.contiguous()
+        src_pitch = src.stride(0)
+        if out is None:
+            shape = (H, W) if (self.cout == 1 and src.ndim == 2) else (H, W, self.cout)
+            out = torch.empty(shape, dtype=torch.uint8, device=src.device)
+        elif not out.is_contiguous() or out.numel() != H * W * self.cout:
+            raise ValueError("out must be a contiguous tensor of H*W*cout bytes")
+        flags = (_lib.LAUNCH_NAIVE if naive else 0) | (_lib.LAUNCH_NO_TMA if no_tma else 0)
+        need_tmp = naive or self.n_segments > 1 or (self.halo > 0 and (W <= 16 or H <= 16))
+        t0 = t1 = ls = None
+        if need_tmp:
+            t0, t1, ls = self.scratch(src.device, W, H)
+        with torch.cuda.device(src.device):
+            L = Launch()
+            L.W, L.H, L.y0, L.y1 = W, H, 0, H
+            L.src = View(src.data_ptr(), src_pitch, 0, H)
+            L.dst = View(out.data_ptr(), W * self.cout, 0, H)
+            if need_tmp:
+                L.tmp[0] = View(t0.data_ptr(), W * 3, 0, H)
+                L.tmp[1] = View(t1.data_ptr(), W * 3, 0, H)
+                L.counters = ls.data_ptr()
+            L.stream = torch.cuda.current_stream().cuda_stream
+            L.tile_h = tile_h
+            L.flags = flags
+            check(lib.b2i_cuda_run(self._p, C.byref(L)))
+        return out
+
+
+_PLAN_CACHE = {}
+
+
+def cuda_run(chain, img: torch.Tensor, out=None, **kw) -> torch.Tensor:
+    """One-shot convenience: plans are cached per (chain description, order, channels)."""
+    run_kw = {k: kw.pop(k) for k in ("naive", "no_tma", "tile_h") if k in kw}
+    ch = as_chain(chain, **kw)
+    _, _, Cn = image_geometry(img)
+    key = (ch.describe(), bytes(ch.c), Cn)
+    plan = _PLAN_CACHE.get(key)
+    if plan is None:
+        plan = _PLAN_CACHE[key] = Plan(ch, Cn)
+    return plan.run(img, out, **run_kw)

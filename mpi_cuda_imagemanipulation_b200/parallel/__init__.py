@@ -1,0 +1,1 @@
+from .runtime import Runtime, topology  # noqa: F401
