@@ -120,7 +120,7 @@ template <int TYPE>
 __device__ void pw_phase(const TileParams& P, const PhaseDesc& ph, uint8_t* sbase, int spitch,
                          int sxorg, int syorg, uint8_t* dbase, int dpitch, int dxorg, int dyorg,
                          const uint8_t* lut) {
-  const int R = P.halo, m = ph.margin, mc = m > 0 ? kApron : 0;
+  const int R = P.halo, m = ph.margin, mc = m > 0 ? kMarginCols : 0;
   const int ux = (kTileW + 2 * mc) >> 2;  // units of 4 pixels per row
   const int rows = P.th + 2 * m;
   const GrayRefCoef gk = gray_ref_coef(P.rgb_order);
@@ -225,7 +225,7 @@ __device__ void stencil_phase(const TileParams& P, const PhaseDesc& ph, const Ti
                               int dxorg, int dyorg, const uint8_t* lut) {
   constexpr int r = K / 2;
   constexpr int RG = SOBEL ? 2 : kRowGroup;
-  const int R = P.halo, m = ph.margin, mc = m > 0 ? kApron : 0;
+  const int R = P.halo, m = ph.margin, mc = m > 0 ? kMarginCols : 0;
   const int strips = ((kTileW + 2 * mc) * C) >> 3;
   const int rows = P.th + 2 * m;
   const int groups = (rows + RG - 1) / RG;
@@ -372,8 +372,8 @@ tile_chain_kernel(const __grid_constant__ TileParams P, const __grid_constant__ 
     mbar_init(&full_bar[0], 1);
     mbar_init(&full_bar[1], 1);
     fence_mbar_init();
-    if (P.use_tma_load) tma_prefetch_desc(&src_map);
-    if (P.use_tma_store) tma_prefetch_desc(&dst_map);
+    if (P.use_tma_load && !(P.debug & 1)) tma_prefetch_desc(&src_map);
+    if (P.use_tma_store && !(P.debug & 1)) tma_prefetch_desc(&dst_map);
   }
   for (int i = tid; i < kMaxLuts * 256 / 4; i += kTileThreads)
     reinterpret_cast<uint32_t*>(luts)[i] = reinterpret_cast<const uint32_t*>(&P.luts[0][0])[i];
@@ -508,8 +508,20 @@ tile_chain_kernel(const __grid_constant__ TileParams P, const __grid_constant__ 
       if (tid == 0) {
         const int xw = (T.tx0 * P.cout) >> 2;
         tma_store_2d(&dst_map, xw, T.ty0 - P.dst_y_begin, stage);
-        if (push_up) tma_store_2d(&push_up_map, xw, T.ty0 - P.push_up_y_begin, stage);
-        if (push_dn) tma_store_2d(&push_dn_map, xw, T.ty0 - P.push_dn_y_begin, stage);
+        // TMA stores clip at the far edge of the tensor only: a negative coordinate faults
+        // (measured, scripts/tma_probe_store.cu). Halo rows are therefore pushed with one-row
+        // boxes, one per staged row that belongs to the halo; only boundary tiles do this.
+        const int spitch = P.buf[BUF_STAGE].pitch;
+        if (push_up) {
+          const int ra = max(T.ty0, P.y0), rb = min(T.ty0 + P.th, P.y0 + P.push_rows);
+          for (int r = ra; r < rb; ++r)
+            tma_store_2d(&push_up_map, xw, r - P.push_up_y_begin, stage + (r - T.ty0) * spitch);
+        }
+        if (push_dn) {
+          const int ra = max(T.ty0, P.y1 - P.push_rows), rb = min(T.ty0 + P.th, P.y1);
+          for (int r = ra; r < rb; ++r)
+            tma_store_2d(&push_dn_map, xw, r - P.push_dn_y_begin, stage + (r - T.ty0) * spitch);
+        }
         tma_store_commit();
       }
     } else {
@@ -556,27 +568,35 @@ tile_chain_kernel(const __grid_constant__ TileParams P, const __grid_constant__ 
   }
 }
 
-cudaError_t launch_tile_chain(const TileParams& P, const CUtensorMap& src_map,
-                              const CUtensorMap& dst_map, const CUtensorMap& push_up_map,
-                              const CUtensorMap& push_dn_map, int grid, cudaStream_t stream) {
-  static thread_local int configured_smem[64] = {0};
+// The kernel may use every byte of opt-in shared memory; set once per device (setting it per
+// launch size would let a small launch lower the limit under a large one).
+static cudaError_t allow_max_smem() {
+  static bool done[64] = {false};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
-  if (dev < 64 && configured_smem[dev] < P.smem_bytes) {
-    e = cudaFuncSetAttribute(tile_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             P.smem_bytes);
-    if (e != cudaSuccess) return e;
-    configured_smem[dev] = P.smem_bytes;
-  }
+  if (dev < 64 && done[dev]) return cudaSuccess;
+  int optin = 0;
+  e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(tile_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin);
+  if (e != cudaSuccess) return e;
+  if (dev < 64) done[dev] = true;
+  return cudaSuccess;
+}
+
+cudaError_t launch_tile_chain(const TileParams& P, const CUtensorMap& src_map,
+                              const CUtensorMap& dst_map, const CUtensorMap& push_up_map,
+                              const CUtensorMap& push_dn_map, int grid, cudaStream_t stream) {
+  cudaError_t e = allow_max_smem();
+  if (e != cudaSuccess) return e;
   tile_chain_kernel<<<grid, kTileThreads, P.smem_bytes, stream>>>(P, src_map, dst_map, push_up_map,
                                                                   push_dn_map);
   return cudaGetLastError();
 }
 
 cudaError_t tile_chain_occupancy(int smem_bytes, int* blocks_per_sm) {
-  cudaError_t e = cudaFuncSetAttribute(tile_chain_kernel,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+  cudaError_t e = allow_max_smem();
   if (e != cudaSuccess) return e;
   return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, tile_chain_kernel,
                                                        kTileThreads, smem_bytes);

@@ -11,13 +11,17 @@
 namespace b2i {
 
 constexpr int kTileW = 256;            // output tile width in pixels
-constexpr int kApron = 8;              // horizontal apron in pixels on each side of a plane
-constexpr int kPlaneW = kTileW + 2 * kApron;  // 272
+// Horizontal apron of a plane in pixels. 16, not 8: TMA wants the first byte of a box on a
+// 16-byte boundary in global memory (a box starting 24 bytes left of a tile faults with "illegal
+// instruction"; measured, scripts/tma_probe.cu), and 16 pixels are 16 or 48 bytes.
+constexpr int kApron = 16;
+constexpr int kMarginCols = 8;         // columns beyond the tile a non-final phase computes per side
+constexpr int kPlaneW = kTileW + 2 * kApron;  // 288
 constexpr int kMaxTileH = 64;
 constexpr int kTileThreads = 256;
 constexpr int kMaxPhases = 6;
 constexpr int kMaxLuts = 4;
-constexpr int kMaxSegHalo = kApron;    // sum of stencil radii one segment can absorb
+constexpr int kMaxSegHalo = kMarginCols;    // sum of stencil radii one segment can absorb
 constexpr int kRowGroup = 4;           // rows a thread walks in a stencil phase
 constexpr int kGhostRows = 8;          // ghost rows above/below a band buffer (>= kMaxSegHalo)
 
@@ -64,6 +68,7 @@ struct TileParams {
   int32_t halo;              // segment halo R: plane row 0 is tile row -R
   int32_t n_phases;
   int32_t rgb_order;
+  int32_t debug;             // bit 0: skip prefetch.tensormap
   int32_t raw_fix_border;    // border rule to paint onto the raw tile (first phase is a stencil), or -1
   // source / destination views for the non-TMA path, and tensor-map row origins
   int32_t use_tma_load, use_tma_store;

@@ -373,6 +373,7 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
   P.n_phases = (int)seg.phases.size();
   P.rgb_order = plan->chain.order == B2I_ORDER_RGB;
   P.raw_fix_border = seg.raw_fix_border;
+  P.debug = env_int("B200IMG_DEBUG", 0);
   for (int k = 0; k < P.n_phases; ++k) P.ph[k] = seg.phases[k];
   memcpy(P.luts, seg.luts, sizeof P.luts);
   // views
@@ -397,9 +398,11 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
   memset(&dst_map, 0, sizeof dst_map);
   memset(&up_map, 0, sizeof up_map);
   memset(&dn_map, 0, sizeof dn_map);
-  P.use_tma_load = !no_tma && encode_map(&src_map, P.src_ptr, P.src_pitch, (int64_t)L.W * seg.cin,
+  const bool no_tma_load = no_tma || env_int("B200IMG_NO_TMA_LOAD", 0);
+  const bool no_tma_store = no_tma || env_int("B200IMG_NO_TMA_STORE", 0);
+  P.use_tma_load = !no_tma_load && encode_map(&src_map, P.src_ptr, P.src_pitch, (int64_t)L.W * seg.cin,
                                          P.src_y_end - P.src_y_begin, kPlaneW * seg.cin, P.raw_rows);
-  P.use_tma_store = !no_tma && encode_map(&dst_map, P.dst_ptr, P.dst_pitch, (int64_t)L.W * seg.cout,
+  P.use_tma_store = !no_tma_store && encode_map(&dst_map, P.dst_ptr, P.dst_pitch, (int64_t)L.W * seg.cout,
                                           y1 - y0, kTileW * seg.cout, th);
   // multi-GPU hooks: waits guard the first segment's ghost-row reads, pushes and signals ride
   // on the last segment's stores
@@ -438,10 +441,10 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
         bool ok = true;
         if (P.push_up_ptr)
           ok = ok && encode_map(&up_map, P.push_up_ptr, P.push_pitch, (int64_t)L.W * seg.cout,
-                                P.push_rows, kTileW * seg.cout, th);
+                                P.push_rows, kTileW * seg.cout, 1);
         if (P.push_dn_ptr)
           ok = ok && encode_map(&dn_map, P.push_dn_ptr, P.push_pitch, (int64_t)L.W * seg.cout,
-                                P.push_rows, kTileW * seg.cout, th);
+                                P.push_rows, kTileW * seg.cout, 1);
         if (!ok) {  // fall back to plain stores for everything
           P.use_tma_store = 0;
         }
@@ -630,7 +633,7 @@ extern "C" int b2i_cuda_run(b2i_plan_t* plan, const b2i_launch_t* Lp) {
   const int n = (int)plan->segs.size();
   // Degenerate images (narrower or shorter than a border fold can reach) and explicit requests
   // go to the reference-style kernels.
-  const bool tiny = plan->halo > 0 && (L.W <= 2 * kApron || L.H <= 2 * kApron);
+  const bool tiny = plan->halo > 0 && (L.W <= 16 || L.H <= 16);
   if ((L.flags & B2I_LAUNCH_NAIVE) || tiny) {
     B2I_CHECK_ARG(L.y0 == 0 && L.y1 == L.H, "the reference-style path runs whole images only");
     B2I_CHECK_ARG(L.tmp[0].ptr && L.tmp[1].ptr, "the reference-style path needs both tmp images");
