@@ -206,6 +206,29 @@ int b2i_cuda_run(b2i_plan_t* plan, const b2i_launch_t* launch);
 int b2i_cuda_run_image(b2i_plan_t* plan, uint64_t src, int64_t src_pitch, uint64_t dst,
                        int64_t dst_pitch, int W, int H, uint64_t tmp0, uint64_t tmp1,
                        uint64_t lut_scratch, void* stream, int flags);
+/* No counterpart in the reference (it cudaMallocs every buffer, kernel.cu:156,173).
+ * Same result as b2i_cuda_run_image, for callers that cannot allocate device memory at the point
+ * of the call: code running inside another framework's execution callback where the host
+ * framework owns the allocator, processes whose device memory is already fully reserved by a
+ * caching allocator, latency-bound loops that cannot take cudaMalloc's device-wide
+ * synchronisation. The two scratch images and the table block that b2i_cuda_run_image takes
+ * from the caller come instead from a fixed array inside the library's device image; the caller
+ * passes only the input and the output. This function calls no cudaMalloc, cudaFree or other
+ * allocating routine.
+ *  - Limit: W*H <= B2I_NOALLOC_MAX_PIXELS (2 Mi pixels, e.g. 1920x1080); larger images are
+ *    rejected with B2I_ERR_UNSUPPORTED and a message naming the limit. The array is
+ *    B2I_NOALLOC_SCRATCH_BYTES (about 12 MiB) and every GPU that loads the library holds it
+ *    until the process exits.
+ *  - The first call on each device looks up the array's device address (and performs the
+ *    kernels' one-time attribute set-up); make that first call before any stream capture.
+ *  - All calls on a device share the one array. A call never depends on what an earlier call
+ *    left in it (the part that must start clean is cleared on the stream, the rest is written
+ *    before it is read), but two calls that overlap on the GPU - different streams, or
+ *    different threads - race on it: serialise them, e.g. by using one stream. */
+#define B2I_NOALLOC_MAX_PIXELS (2 * 1024 * 1024)
+#define B2I_NOALLOC_SCRATCH_BYTES (2 * 3 * B2I_NOALLOC_MAX_PIXELS + 256 * B2I_MAX_OPS)
+int b2i_cuda_run_image_noalloc(b2i_plan_t* plan, uint64_t src, int64_t src_pitch, uint64_t dst,
+                               int64_t dst_pitch, int W, int H, void* stream, int flags);
 int b2i_cuda_device_count(void);
 /* Host image in, host image out on one GPU: upload, `iters` runs (one warm-up first when
  * iters > 1), download. kernel_ms is the device-event time of one run, total_ms the wall time
