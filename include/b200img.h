@@ -272,6 +272,33 @@ int b2i_ctx_run_cli(int gpus, int root, const b2i_chain_t* chain, const uint8_t*
                     int C, uint8_t* dst, int iters, int flags, int resident, double* kernel_ms,
                     double* total_ms, char* report, size_t report_len);
 
+/* ---- multi-process plumbing (csrc/runtime/ipc.cu): one process per GPU, as under torchrun ---- */
+
+/* Device memory other processes can map; the 64-byte handle goes over any host channel
+ * (torch.distributed here) and is opened by the peers. Image bytes never take that channel. */
+int b2i_ipc_alloc(size_t bytes, uint64_t* ptr, uint8_t* handle64);
+int b2i_ipc_open(const uint8_t* handle64, uint64_t* ptr);
+int b2i_ipc_close(uint64_t ptr);
+int b2i_dev_free(uint64_t ptr);
+/* Pins a host range (e.g. a POSIX shared-memory mapping every rank sees). */
+int b2i_host_register(void* p, size_t bytes);
+int b2i_host_unregister(void* p);
+/* Stream-ordered epoch flags, the device-side replacement of MPI_Barrier (kernel.cu:127,133):
+ * wait until n flags (device addresses, 0 = skip) reach `epoch` / set n flags to `epoch`. */
+int b2i_cuda_wait_flags(const uint64_t* flags, int n, uint32_t epoch, uint64_t status,
+                        uint64_t timeout_ns, void* stream);
+int b2i_cuda_set_flags(const uint64_t* flags, int n, uint32_t epoch, void* stream);
+/* K steps of one band launch from C (one kernel launch of host cost per step), epochs rising
+ * from epoch_base+1; the root rank passes the other ranks' done flags to wait on each step. */
+int b2i_cuda_run_steps(b2i_plan_t* plan, const b2i_launch_t* launch, int steps, uint32_t epoch_base,
+                       const uint64_t* wait_flags, int n_wait);
+/* `passes` applications of a chain on a resident band, ping-ponging between the two launch
+ * descriptions, halo flags waited/signalled with epochs epoch_base+p / epoch_base+p+1. */
+int b2i_cuda_run_resident_steps(b2i_plan_t* plan, const b2i_launch_t* even, const b2i_launch_t* odd,
+                                int passes, uint32_t epoch_base);
+int b2i_cuda_memcpy2d(uint64_t dst, size_t dpitch, uint64_t src, size_t spitch, size_t width,
+                      size_t height, int kind /*0 H2D, 1 D2H, 2 D2D*/, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -175,3 +175,18 @@ _sig("b2i_cuda_run_host_image", C.c_int, _P(ChainStruct), u8p, C.c_int, C.c_int,
 NOALLOC_MAX_PIXELS = 2 * 1024 * 1024
 _sig("b2i_cuda_run_image_noalloc", C.c_int, C.c_void_p, C.c_uint64, C.c_int64, C.c_uint64, C.c_int64,
      C.c_int, C.c_int, C.c_void_p, C.c_int)
+
+# ---- multi-process plumbing ------------------------------------------------------------------------
+_sig("b2i_ipc_alloc", C.c_int, C.c_size_t, _P(C.c_uint64), C.c_char_p)
+_sig("b2i_ipc_open", C.c_int, C.c_char_p, _P(C.c_uint64))
+_sig("b2i_ipc_close", C.c_int, C.c_uint64)
+_sig("b2i_dev_free", C.c_int, C.c_uint64)
+_sig("b2i_host_register", C.c_int, C.c_void_p, C.c_size_t)
+_sig("b2i_host_unregister", C.c_int, C.c_void_p)
+_sig("b2i_cuda_wait_flags", C.c_int, _P(C.c_uint64), C.c_int, C.c_uint32, C.c_uint64, C.c_uint64,
+     C.c_void_p)
+_sig("b2i_cuda_set_flags", C.c_int, _P(C.c_uint64), C.c_int, C.c_uint32, C.c_void_p)
+_sig("b2i_cuda_run_steps", C.c_int, C.c_void_p, _P(Launch), C.c_int, C.c_uint32, _P(C.c_uint64), C.c_int)
+_sig("b2i_cuda_run_resident_steps", C.c_int, C.c_void_p, _P(Launch), _P(Launch), C.c_int, C.c_uint32)
+_sig("b2i_cuda_memcpy2d", C.c_int, C.c_uint64, C.c_size_t, C.c_uint64, C.c_size_t, C.c_size_t, C.c_size_t,
+     C.c_int, C.c_void_p)
