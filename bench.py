@@ -27,6 +27,8 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# NCCL writes its version banner to stdout by default; stdout carries exactly one JSON line here
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 W8K, H8K = 7680, 4320
 CHAIN = "kernel_cu"
