@@ -168,6 +168,72 @@ __device__ void pw_phase(const TileParams& P, const PhaseDesc& ph, uint8_t* sbas
   }
 }
 
+// Gray conversion of a plane, 8 pixels per item: three LDS.64 in, one STS.64 out, the source and
+// destination addresses advanced incrementally (the first version of this phase spent more
+// instructions on indexing 4-pixel units than on the conversion itself: ncu, profiles/).
+template <int TYPE, bool LUT>
+__device__ __forceinline__ void gray8(const uint8_t* s, uint8_t* d, const GrayRefCoef& gk, int rgb,
+                                      const uint8_t* lut) {
+  const uint2 v0 = *reinterpret_cast<const uint2*>(s), v1 = *reinterpret_cast<const uint2*>(s + 8),
+              v2 = *reinterpret_cast<const uint2*>(s + 16);
+  const uint32_t w0 = v0.x, w1 = v0.y, w2 = v1.x, w3 = v1.y, w4 = v2.x, w5 = v2.y;
+  uint32_t g[8];
+  if (TYPE == PH_GRAY_REF) {
+    g[0] = gray_ref_f23(byte_to_f23<0>(w0), byte_to_f23<1>(w0), byte_to_f23<2>(w0), gk);
+    g[1] = gray_ref_f23(byte_to_f23<3>(w0), byte_to_f23<0>(w1), byte_to_f23<1>(w1), gk);
+    g[2] = gray_ref_f23(byte_to_f23<2>(w1), byte_to_f23<3>(w1), byte_to_f23<0>(w2), gk);
+    g[3] = gray_ref_f23(byte_to_f23<1>(w2), byte_to_f23<2>(w2), byte_to_f23<3>(w2), gk);
+    g[4] = gray_ref_f23(byte_to_f23<0>(w3), byte_to_f23<1>(w3), byte_to_f23<2>(w3), gk);
+    g[5] = gray_ref_f23(byte_to_f23<3>(w3), byte_to_f23<0>(w4), byte_to_f23<1>(w4), gk);
+    g[6] = gray_ref_f23(byte_to_f23<2>(w4), byte_to_f23<3>(w4), byte_to_f23<0>(w5), gk);
+    g[7] = gray_ref_f23(byte_to_f23<1>(w5), byte_to_f23<2>(w5), byte_to_f23<3>(w5), gk);
+  } else {
+    g[0] = gray_cv_px(w0 & 0xFF, (w0 >> 8) & 0xFF, (w0 >> 16) & 0xFF, rgb);
+    g[1] = gray_cv_px(w0 >> 24, w1 & 0xFF, (w1 >> 8) & 0xFF, rgb);
+    g[2] = gray_cv_px((w1 >> 16) & 0xFF, w1 >> 24, w2 & 0xFF, rgb);
+    g[3] = gray_cv_px((w2 >> 8) & 0xFF, (w2 >> 16) & 0xFF, w2 >> 24, rgb);
+    g[4] = gray_cv_px(w3 & 0xFF, (w3 >> 8) & 0xFF, (w3 >> 16) & 0xFF, rgb);
+    g[5] = gray_cv_px(w3 >> 24, w4 & 0xFF, (w4 >> 8) & 0xFF, rgb);
+    g[6] = gray_cv_px((w4 >> 16) & 0xFF, w4 >> 24, w5 & 0xFF, rgb);
+    g[7] = gray_cv_px((w5 >> 8) & 0xFF, (w5 >> 16) & 0xFF, w5 >> 24, rgb);
+  }
+  if (LUT) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) g[i] = lut[g[i] & 0xFF];
+  }
+  *reinterpret_cast<uint2*>(d) = make_uint2(pack4_lo(g[0], g[1], g[2], g[3]), pack4_lo(g[4], g[5], g[6], g[7]));
+}
+
+template <int TYPE, bool LUT>
+__device__ void gray_phase(const TileParams& P, const PhaseDesc& ph, const uint8_t* sbase, int spitch,
+                           int sxorg, int syorg, uint8_t* dbase, int dpitch, int dxorg, int dyorg,
+                           const uint8_t* lut) {
+  const int R = P.halo, m = ph.margin, mc = m > 0 ? kMarginCols : 0;
+  const int ux = (kTileW + 2 * mc) >> 3;  // items of 8 pixels per row: 32 or 34
+  const int n = ux * (P.th + 2 * m);
+  const GrayRefCoef gk = gray_ref_coef(P.rgb_order);
+  const int rgb = P.rgb_order;
+  int idx = threadIdx.x;
+  const int row0 = idx / ux;
+  int col = idx - row0 * ux;
+  const int drow = kTileThreads / ux, dcol = kTileThreads - drow * ux;
+  const uint8_t* ps = sbase + (R - m - syorg + row0) * spitch + (kApron - mc - sxorg) * 3 + col * 24;
+  uint8_t* pd = dbase + (R - m - dyorg + row0) * dpitch + (kApron - mc - dxorg) + col * 8;
+  const int step_s = drow * spitch + dcol * 24, step_d = drow * dpitch + dcol * 8;
+  const int wrap_s = spitch - ux * 24, wrap_d = dpitch - ux * 8;
+  for (; idx < n; idx += kTileThreads) {
+    gray8<TYPE, LUT>(ps, pd, gk, rgb, lut);
+    col += dcol;
+    ps += step_s;
+    pd += step_d;
+    if (col >= ux) {
+      col -= ux;
+      ps += wrap_s;
+      pd += wrap_d;
+    }
+  }
+}
+
 // ---- stencil phases (smem -> smem) ----------------------------------------------------------------
 
 // Bytes [o, o+4) of the 24-byte row window a[0..5].
@@ -217,24 +283,43 @@ __device__ __forceinline__ void tap_row(const uint32_t (&a)[6], const uint32_t* 
   tap_px<C, K, SOBEL, 7>(a, w, w2, acc[7], acc2[7]);
 }
 
-// One thread: an 8-byte-wide strip, kRowGroup output rows, K + kRowGroup - 1 input rows each
-// read once (three LDS.64), all taps through dp4a.
+// One thread: an 8-byte-wide strip, RG output rows, K + RG - 1 input rows each read once (three
+// LDS.64), all taps through dp4a. Weights are pulled into registers once per phase; everything
+// that is uniform per phase (REF, LUT, expand, scaling) is decided outside the row loop.
 template <int C, int K, bool SOBEL>
 __device__ void stencil_phase(const TileParams& P, const PhaseDesc& ph, const Tile& T,
                               const uint8_t* sbase, int spitch, uint8_t* dbase, int dpitch,
                               int dxorg, int dyorg, const uint8_t* lut) {
   constexpr int r = K / 2;
   constexpr int RG = SOBEL ? 2 : kRowGroup;
+  constexpr int ND = DpCount<C, K>::value;
   const int R = P.halo, m = ph.margin, mc = m > 0 ? kMarginCols : 0;
   const int strips = ((kTileW + 2 * mc) * C) >> 3;
   const int rows = P.th + 2 * m;
   const int groups = (rows + RG - 1) / RG;
   const bool ref = ph.border == B2I_BORDER_REF;
   const bool scale = (ph.shift | ph.bias) != 0;
-  for (int item = threadIdx.x; item < strips * groups; item += kTileThreads) {
+  const bool expand = ph.expand != 0;
+  const int shift = ph.shift, bias = ph.bias;
+  uint32_t w[K][ND], w2[SOBEL ? 3 : 1][ND];
+  uint32_t rowmask = 0;  // stencil rows that have a non-zero weight (emboss5: one tap per row)
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    uint32_t any = 0;
+#pragma unroll
+    for (int d = 0; d < ND; ++d) {
+      w[k][d] = ph.wpk[k][d];
+      any |= ph.wpk[k][d];
+      if (SOBEL) w2[k][d] = ph.wpk2[k][d];
+    }
+    if (any || K == 3) rowmask |= 1u << k;
+  }
+  const int n_items = strips * groups;
+  for (int item = threadIdx.x; item < n_items; item += kTileThreads) {
     const int g = item / strips, strip = item - g * strips;
     const int bc = (kApron - mc) * C + strip * 8;  // plane byte column of the strip
     const int pr0 = R - m + g * RG;                 // plane row of the first output row
+    const int nvalid = rows - g * RG;               // output rows of this group inside the region
     int acc[RG][8], acc2[SOBEL ? RG : 1][8];
     uint32_t centre[RG][2];
 #pragma unroll
@@ -244,28 +329,30 @@ __device__ void stencil_phase(const TileParams& P, const PhaseDesc& ph, const Ti
         acc[o][i] = 0;
         if (SOBEL) acc2[o][i] = 0;
       }
-    const uint8_t* srow = sbase + (size_t)(pr0 - r) * spitch + bc - 8;
+    const uint8_t* srow = sbase + (pr0 - r) * spitch + bc - 8;
 #pragma unroll
     for (int j = 0; j < K + RG - 1; ++j) {
       uint32_t a[6];
-      const uint2 v0 = *reinterpret_cast<const uint2*>(srow + (size_t)j * spitch);
-      const uint2 v1 = *reinterpret_cast<const uint2*>(srow + (size_t)j * spitch + 8);
-      const uint2 v2 = *reinterpret_cast<const uint2*>(srow + (size_t)j * spitch + 16);
+      const uint2 v0 = *reinterpret_cast<const uint2*>(srow + j * spitch);
+      const uint2 v1 = *reinterpret_cast<const uint2*>(srow + j * spitch + 8);
+      const uint2 v2 = *reinterpret_cast<const uint2*>(srow + j * spitch + 16);
       a[0] = v0.x; a[1] = v0.y; a[2] = v1.x; a[3] = v1.y; a[4] = v2.x; a[5] = v2.y;
 #pragma unroll
       for (int o = 0; o < RG; ++o) {
-        const int k = j - o;  // stencil row this input row is for output row o
+        constexpr int dummy = 0;
+        (void)dummy;
+        const int k = j - o;  // stencil row this input row is for output row o (compile time)
         if (k < 0 || k >= K) continue;
         if (k == r) {
           centre[o][0] = a[2];
           centre[o][1] = a[3];
         }
         if (SOBEL) {
-          tap_row<C, K, true>(a, ph.wpk[k], ph.wpk2[k], acc[o], acc2[o]);
-        } else {
-          // rows of zero weights (emboss5 has one tap per row, the 3x3 kernels none) are skipped
-          if ((ph.wpk[k][0] | ph.wpk[k][1] | ph.wpk[k][2]) != 0)
-            tap_row<C, K, false>(a, ph.wpk[k], ph.wpk[k], acc[o], acc[o]);
+          tap_row<C, K, true>(a, w[k], w2[k], acc[o], acc2[o]);
+        } else if (K == 3) {
+          tap_row<C, K, false>(a, w[k], w[k], acc[o], acc[o]);
+        } else if (rowmask & (1u << k)) {
+          tap_row<C, K, false>(a, w[k], w[k], acc[o], acc[o]);
         }
       }
     }
@@ -284,46 +371,53 @@ __device__ void stencil_phase(const TileParams& P, const PhaseDesc& ph, const Ti
         }
       }
     }
+    const int gy0 = T.ty0 - R + pr0;
+    uint32_t res[RG][2];
 #pragma unroll
     for (int o = 0; o < RG; ++o) {
-      const int pr = pr0 + o;
-      if (pr >= R - m + rows) break;
       if (SOBEL) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) acc[o][i] = abs(acc[o][i]) + abs(acc2[o][i]);
       } else if (scale) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) acc[o][i] = (acc[o][i] + ph.bias) >> ph.shift;
+        for (int i = 0; i < 8; ++i) acc[o][i] = (acc[o][i] + bias) >> shift;
       }
       uint32_t r0 = sat_pack4(acc[o][0], acc[o][1], acc[o][2], acc[o][3]);
       uint32_t r1 = sat_pack4(acc[o][4], acc[o][5], acc[o][6], acc[o][7]);
       if (ref) {
-        const int gy = T.ty0 - R + pr;
+        const int gy = gy0 + o;
         const bool row_ok = gy >= r + 1 && gy <= P.H - r - 1;
         const uint32_t mm0 = row_ok ? m0 : 0u, mm1 = row_ok ? m1 : 0u;
         r0 = (r0 & mm0) | (centre[o][0] & ~mm0);
         r1 = (r1 & mm1) | (centre[o][1] & ~mm1);
       }
-      if (lut) {
-        r0 = lut4(lut, r0);
-        r1 = lut4(lut, r1);
+      res[o][0] = r0;
+      res[o][1] = r1;
+    }
+    if (lut) {
+#pragma unroll
+      for (int o = 0; o < RG; ++o) {
+        res[o][0] = lut4(lut, res[o][0]);
+        res[o][1] = lut4(lut, res[o][1]);
       }
-      if (ph.expand) {  // C == 1: 8 gray pixels -> 24 bytes of BGR (kernel.cu:210 fused here)
-        uint8_t* d = dbase + (size_t)(pr - dyorg) * dpitch + (bc - dxorg) * 3;
-        uint2 e0, e1, e2;
-        e0.x = __byte_perm(r0, 0, 0x1000);
-        e0.y = __byte_perm(r0, 0, 0x2211);
-        e1.x = __byte_perm(r0, 0, 0x3332);
-        e1.y = __byte_perm(r1, 0, 0x1000);
-        e2.x = __byte_perm(r1, 0, 0x2211);
-        e2.y = __byte_perm(r1, 0, 0x3332);
-        reinterpret_cast<uint2*>(d)[0] = e0;
-        reinterpret_cast<uint2*>(d)[1] = e1;
-        reinterpret_cast<uint2*>(d)[2] = e2;
-      } else {
-        uint8_t* d = dbase + (size_t)(pr - dyorg) * dpitch + (bc - dxorg * C);
-        *reinterpret_cast<uint2*>(d) = make_uint2(r0, r1);
+    }
+    if (expand) {  // C == 1: 8 gray pixels -> 24 bytes of BGR (kernel.cu:210 fused here)
+      uint8_t* d = dbase + (pr0 - dyorg) * dpitch + (bc - dxorg) * 3;
+#pragma unroll
+      for (int o = 0; o < RG; ++o) {
+        if (o < nvalid) {
+          const uint32_t r0 = res[o][0], r1 = res[o][1];
+          uint2* q = reinterpret_cast<uint2*>(d + o * dpitch);
+          q[0] = make_uint2(__byte_perm(r0, 0, 0x1000), __byte_perm(r0, 0, 0x2211));
+          q[1] = make_uint2(__byte_perm(r0, 0, 0x3332), __byte_perm(r1, 0, 0x1000));
+          q[2] = make_uint2(__byte_perm(r1, 0, 0x2211), __byte_perm(r1, 0, 0x3332));
+        }
       }
+    } else {
+      uint8_t* d = dbase + (pr0 - dyorg) * dpitch + (bc - dxorg * C);
+#pragma unroll
+      for (int o = 0; o < RG; ++o)
+        if (o < nvalid) *reinterpret_cast<uint2*>(d + o * dpitch) = make_uint2(res[o][0], res[o][1]);
     }
   }
 }
@@ -467,10 +561,12 @@ tile_chain_kernel(const __grid_constant__ TileParams P, const __grid_constant__ 
       }
       switch (ph.type) {
         case PH_GRAY_REF:
-          pw_phase<PH_GRAY_REF>(P, ph, sbase, sb.pitch, sb.xorg, sb.yorg, dbase, db.pitch, db.xorg, db.yorg, lut);
+          if (lut) gray_phase<PH_GRAY_REF, true>(P, ph, sbase, sb.pitch, sb.xorg, sb.yorg, dbase, db.pitch, db.xorg, db.yorg, lut);
+          else gray_phase<PH_GRAY_REF, false>(P, ph, sbase, sb.pitch, sb.xorg, sb.yorg, dbase, db.pitch, db.xorg, db.yorg, lut);
           break;
         case PH_GRAY_CV:
-          pw_phase<PH_GRAY_CV>(P, ph, sbase, sb.pitch, sb.xorg, sb.yorg, dbase, db.pitch, db.xorg, db.yorg, lut);
+          if (lut) gray_phase<PH_GRAY_CV, true>(P, ph, sbase, sb.pitch, sb.xorg, sb.yorg, dbase, db.pitch, db.xorg, db.yorg, lut);
+          else gray_phase<PH_GRAY_CV, false>(P, ph, sbase, sb.pitch, sb.xorg, sb.yorg, dbase, db.pitch, db.xorg, db.yorg, lut);
           break;
         case PH_COPY:
           pw_phase<PH_COPY>(P, ph, sbase, sb.pitch, sb.xorg, sb.yorg, dbase, db.pitch, db.xorg, db.yorg, lut);
