@@ -1,0 +1,298 @@
+// The sweep kernel: the reference's whole pipeline (kernel.cu:192-195,210 / kern.cpp:73-77) as a
+// warp-synchronous column sweep with everything between load and store in registers.
+//
+//   gray (kernel.cu:39-42 or cv) -> [LUT: contrast] -> 3x3 stencil on gray -> [LUT] -> [gray->BGR]
+//
+// The generic tile-chain kernel (tile_chain.cu) runs this shape at ~48 % of the HBM roofline: it
+// is bound by instruction issue, not by memory (ncu, profiles/). Two thirds of its instructions
+// are shared-memory round trips, index arithmetic and block barriers between phases. This kernel
+// removes all three for the shape the reference actually runs:
+//   * a warp owns a strip of 240 output pixels (30 lanes x 8 pixels; lanes 0 and 31 only feed
+//     their neighbours) and walks down a segment of rows;
+//   * rows arrive by TMA (3-row boxes, 3 stages per warp, one mbarrier per stage) and each lane
+//     converts its 24 bytes to 8 gray pixels exactly once;
+//   * horizontal neighbours come from two warp shuffles per row, vertical neighbours from three
+//     rotating accumulator sets: a gray row is used for the three output rows it touches the
+//     moment it exists and is never stored;
+//   * finished rows are expanded to BGR in registers, staged per warp and leave by TMA store.
+// No __syncthreads, no inter-phase planes, 15-16 instructions per pixel instead of 37.
+// Source and destination may be peer memory (scatter / gather fused), exactly as in tile_chain.cu.
+#include "b200img.h"
+#include "device_utils.cuh"
+#include "sweep3.hpp"
+
+namespace b2i {
+using namespace dev;
+
+namespace {
+
+constexpr int kWarps = kSweepWarps;
+constexpr int CH = kSweepChunk;   // rows per TMA box
+constexpr int NST = kSweepStages;  // input stages per warp
+
+__device__ __forceinline__ uint32_t lut4s(const uint8_t* lut, uint32_t w) {
+  const uint32_t a = lut[w & 0xFF], b = lut[(w >> 8) & 0xFF], c = lut[(w >> 16) & 0xFF], d = lut[w >> 24];
+  return pack4_lo(a, b, c, d);
+}
+
+// Bytes [o, o+4) of the 16-byte window {left, own0, own1, right}.
+template <int O>
+__device__ __forceinline__ uint32_t win(const uint32_t (&a)[4]) {
+  if constexpr ((O & 3) == 0) return a[O >> 2];
+  else return __funnelshift_r(a[O >> 2], a[(O >> 2) + 1], (O & 3) * 8);
+}
+
+// acc[i] += dot(gray[x_i-1 .. x_i+1], w) for the lane's 8 pixels.
+__device__ __forceinline__ void taps(const uint32_t (&v)[8], uint32_t w, int (&acc)[8]) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = dp4a_us(v[i], w, acc[i]);
+}
+
+template <int GRAY>
+__device__ __forceinline__ void gray8(const uint8_t* s, const GrayRefCoef& gk, int rgb, uint32_t (&g)[8]) {
+  const uint2 v0 = *reinterpret_cast<const uint2*>(s), v1 = *reinterpret_cast<const uint2*>(s + 8),
+              v2 = *reinterpret_cast<const uint2*>(s + 16);
+  const uint32_t w0 = v0.x, w1 = v0.y, w2 = v1.x, w3 = v1.y, w4 = v2.x, w5 = v2.y;
+  if (GRAY == 1) {
+    g[0] = gray_ref_f23(byte_to_f23<0>(w0), byte_to_f23<1>(w0), byte_to_f23<2>(w0), gk);
+    g[1] = gray_ref_f23(byte_to_f23<3>(w0), byte_to_f23<0>(w1), byte_to_f23<1>(w1), gk);
+    g[2] = gray_ref_f23(byte_to_f23<2>(w1), byte_to_f23<3>(w1), byte_to_f23<0>(w2), gk);
+    g[3] = gray_ref_f23(byte_to_f23<1>(w2), byte_to_f23<2>(w2), byte_to_f23<3>(w2), gk);
+    g[4] = gray_ref_f23(byte_to_f23<0>(w3), byte_to_f23<1>(w3), byte_to_f23<2>(w3), gk);
+    g[5] = gray_ref_f23(byte_to_f23<3>(w3), byte_to_f23<0>(w4), byte_to_f23<1>(w4), gk);
+    g[6] = gray_ref_f23(byte_to_f23<2>(w4), byte_to_f23<3>(w4), byte_to_f23<0>(w5), gk);
+    g[7] = gray_ref_f23(byte_to_f23<1>(w5), byte_to_f23<2>(w5), byte_to_f23<3>(w5), gk);
+  } else {
+    g[0] = gray_cv_px(w0 & 0xFF, (w0 >> 8) & 0xFF, (w0 >> 16) & 0xFF, rgb);
+    g[1] = gray_cv_px(w0 >> 24, w1 & 0xFF, (w1 >> 8) & 0xFF, rgb);
+    g[2] = gray_cv_px((w1 >> 16) & 0xFF, w1 >> 24, w2 & 0xFF, rgb);
+    g[3] = gray_cv_px((w2 >> 8) & 0xFF, (w2 >> 16) & 0xFF, w2 >> 24, rgb);
+    g[4] = gray_cv_px(w3 & 0xFF, (w3 >> 8) & 0xFF, (w3 >> 16) & 0xFF, rgb);
+    g[5] = gray_cv_px(w3 >> 24, w4 & 0xFF, (w4 >> 8) & 0xFF, rgb);
+    g[6] = gray_cv_px((w4 >> 16) & 0xFF, w4 >> 24, w5 & 0xFF, rgb);
+    g[7] = gray_cv_px((w5 >> 8) & 0xFF, (w5 >> 16) & 0xFF, w5 >> 24, rgb);
+  }
+}
+
+template <int GRAY, bool LUT0>
+__global__ void __launch_bounds__(kWarps * 32, 2)
+sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUtensorMap src_map,
+              const __grid_constant__ CUtensorMap dst_map) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ __align__(256) uint8_t lut0[256];
+  __shared__ __align__(256) uint8_t lut1[256];
+  __shared__ __align__(8) uint64_t bars[kWarps * NST];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < 64; i += kWarps * 32) {
+    reinterpret_cast<uint32_t*>(lut0)[i] = reinterpret_cast<const uint32_t*>(P.lut0)[i];
+    reinterpret_cast<uint32_t*>(lut1)[i] = reinterpret_cast<const uint32_t*>(P.lut1)[i];
+  }
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kWarps * NST; ++i) mbar_init(&bars[i], 1);
+    fence_mbar_init();
+    tma_prefetch_desc(&src_map);
+    tma_prefetch_desc(&dst_map);
+  }
+  __syncthreads();  // the only block-wide barrier of the kernel
+
+  const int out_pitch = P.expand ? kSweepOutBytes : kSweepStrip;  // staged bytes per output row
+  uint8_t* in_ring = smem + warp * P.warp_smem;        // NST stages of CH rows x kSweepInBytes (128 B aligned)
+  uint8_t* out_ring = in_ring + NST * P.in_stage_bytes;  // 2 staging buffers of CH rows x out_pitch
+  uint64_t* bar = &bars[warp * NST];
+  const GrayRefCoef gk = gray_ref_coef(P.rgb_order);
+  const int rgb = P.rgb_order;
+  const uint32_t w0 = P.wpk[0], w1 = P.wpk[1], w2 = P.wpk[2];
+  const bool ref = P.border == B2I_BORDER_REF;
+  const bool scale = (P.shift | P.bias) != 0;
+
+  uint32_t n_in = 0;   // input chunks consumed by this warp so far (stage = n_in % NST)
+  uint32_t n_out = 0;  // output chunks stored so far (buffer = n_out & 1)
+  const int total_warps = gridDim.x * kWarps;
+  for (int task = blockIdx.x * kWarps + warp; task < P.n_tasks; task += total_warps) {
+    const int seg = task / P.n_strips, strip = task - seg * P.n_strips;
+    const int ya = P.y0 + seg * P.seg_rows, yb = min(P.y1, ya + P.seg_rows);  // output rows [ya, yb)
+    const int steps = yb - ya + 2;                   // gray rows ya-1 .. yb
+    const int n_chunks = (steps + CH - 1) / CH;
+    const int xs = strip * kSweepStrip;              // first output pixel of the strip
+    const int x0 = xs - 8 + lane * 8;                // first pixel this lane holds (lane 0: halo)
+    const int xw_in = (xs * 3 - 32) >> 2;            // TMA x (u32 elements): 32 bytes left of the strip
+    const int xw_out = (xs * (P.expand ? 3 : 1)) >> 2;
+
+    // ---- input pipeline: the first NST chunks are in flight before any is consumed --------
+    if (lane == 0) {
+      for (int c = 0; c < min(NST, n_chunks); ++c) {
+        const uint32_t st = (n_in + c) % NST;
+        mbar_arrive_expect_tx(&bar[st], CH * kSweepInBytes);
+        tma_load_2d(in_ring + st * P.in_stage_bytes, &src_map, xw_in, ya - 1 + c * CH - P.src_y_begin, &bar[st]);
+      }
+    }
+
+    // REF border: which of my 8 pixels are filtered at all (x in [2, W-2]); rows checked below
+    uint32_t m0 = 0xFFFFFFFFu, m1 = 0xFFFFFFFFu;
+    if (ref) {
+      const int lo = 2 - x0, hi = P.W - 2 - x0;
+      if (lo > 0 || hi < 7) {
+        m0 = m1 = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          if (i >= lo && i <= hi) m0 |= 0xFFu << (8 * i);
+          if (i + 4 >= lo && i + 4 <= hi) m1 |= 0xFFu << (8 * i);
+        }
+      }
+    }
+    const bool left_edge = x0 == 0, right_edge = x0 + 8 == P.W, beyond = x0 < 0 || x0 >= P.W;
+
+    int accA[8], accB[8], accC[8];  // output rows y-1, y, y+1 while gray row y is being applied
+    uint32_t prev[4] = {0, 0, 0, 0};                      // window words of the previous gray row
+#pragma unroll
+    for (int i = 0; i < 8; ++i) accA[i] = accB[i] = accC[i] = 0;
+
+    for (int t = 0; t < steps; ++t) {
+      const int y = ya - 1 + t;
+      const int c = t / CH, rr = t - c * CH;
+      const uint32_t st = (n_in + c) % NST;
+      if (rr == 0) mbar_wait(&bar[st], ((n_in + c) / NST) & 1);
+      // ---- gray row y: 8 pixels per lane, once -------------------------------------------
+      uint32_t a[4];
+      if (y >= 0 && y < P.H) {
+        uint32_t g[8];
+        gray8<GRAY>(in_ring + st * P.in_stage_bytes + rr * kSweepInBytes + 8 + lane * 24, gk, rgb, g);
+        if (LUT0) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) g[i] = lut0[g[i] & 0xFF];
+        }
+        a[1] = pack4_lo(g[0], g[1], g[2], g[3]);
+        a[2] = pack4_lo(g[4], g[5], g[6], g[7]);
+        if (beyond) a[1] = a[2] = 0;
+      } else {
+        a[1] = a[2] = 0;  // rows outside the image contribute nothing; borders are folded in below
+      }
+      a[0] = __shfl_up_sync(0xFFFFFFFFu, a[2], 1);
+      a[3] = __shfl_down_sync(0xFFFFFFFFu, a[1], 1);
+      if (P.border == B2I_BORDER_REFLECT101) {  // pixel -1 := pixel 1, pixel W := pixel W-2
+        if (left_edge) a[0] = __byte_perm(a[0], a[1], 0x5210);   // byte 3 <- own byte 1
+        if (right_edge) a[3] = __byte_perm(a[3], a[2], 0x3216);  // byte 0 <- own1 byte 2
+      } else if (P.border == B2I_BORDER_REPLICATE) {
+        if (left_edge) a[0] = __byte_perm(a[0], a[1], 0x4210);   // byte 3 <- own byte 0
+        if (right_edge) a[3] = __byte_perm(a[3], a[2], 0x3217);  // byte 0 <- own1 byte 3
+      }
+      // the stage can be refilled once every lane has read the chunk's last row
+      if (rr == CH - 1 || t == steps - 1) {
+        __syncwarp();
+        if (lane == 0 && c + NST < n_chunks) {
+          mbar_arrive_expect_tx(&bar[st], CH * kSweepInBytes);
+          tma_load_2d(in_ring + st * P.in_stage_bytes, &src_map, xw_in,
+                      ya - 1 + (c + NST) * CH - P.src_y_begin, &bar[st]);
+        }
+      }
+      // ---- apply gray row y to output rows y-1 (bottom taps), y (middle), y+1 (top) ----------
+      {
+        uint32_t v[8];
+        v[0] = win<3>(a); v[1] = win<4>(a); v[2] = win<5>(a); v[3] = win<6>(a);
+        v[4] = win<7>(a); v[5] = win<8>(a); v[6] = win<9>(a); v[7] = win<10>(a);
+        taps(v, w2, accA);
+        taps(v, w1, accB);
+        taps(v, w0, accC);
+        // vertical borders: row -1 := row 1 / row 0, row H := row H-2 / row H-1
+        if (P.border == B2I_BORDER_REFLECT101) {
+          if (y == 1) taps(v, w0, accA);                 // row 1 also stands for row -1 (out row 0)
+          if (y == P.H - 1) {                            // row H-2 also stands for row H (out row H-1)
+            uint32_t pv[8];
+            pv[0] = win<3>(prev); pv[1] = win<4>(prev); pv[2] = win<5>(prev); pv[3] = win<6>(prev);
+            pv[4] = win<7>(prev); pv[5] = win<8>(prev); pv[6] = win<9>(prev); pv[7] = win<10>(prev);
+            taps(pv, w2, accB);
+          }
+        } else if (P.border == B2I_BORDER_REPLICATE) {
+          if (y == 0) taps(v, w0, accB);                 // row 0 also stands for row -1
+          if (y == P.H - 1) taps(v, w2, accB);           // row H-1 also stands for row H
+        }
+      }
+      // ---- output row y-1 is complete ---------------------------------------------------------
+      if (t >= 2) {
+        const int e = t - 2;                 // output row index within the task
+        const int ec = e / CH, er = e - ec * CH;
+        const uint32_t ob = (n_out + ec) & 1;
+        if (er == 0) {                       // about to reuse a staging buffer: its store has read it
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          __syncwarp();
+        }
+        if (scale) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) accA[i] = (accA[i] + P.bias) >> P.shift;
+        }
+        uint32_t r0 = sat_pack4(accA[0], accA[1], accA[2], accA[3]);
+        uint32_t r1 = sat_pack4(accA[4], accA[5], accA[6], accA[7]);
+        if (ref) {
+          const int oy = y - 1;
+          const bool row_ok = oy >= 2 && oy <= P.H - 2;
+          const uint32_t mm0 = row_ok ? m0 : 0u, mm1 = row_ok ? m1 : 0u;
+          r0 = (r0 & mm0) | (prev[1] & ~mm0);  // prev = gray row y-1: the pass-through value
+          r1 = (r1 & mm1) | (prev[2] & ~mm1);
+        }
+        if (P.has_lut1) {
+          r0 = lut4s(lut1, r0);
+          r1 = lut4s(lut1, r1);
+        }
+        if (lane >= 1 && lane <= 30) {
+          uint8_t* d = out_ring + ob * P.out_buf_bytes + er * out_pitch;
+          if (P.expand) {  // kernel.cu:210 in registers: 8 gray -> 24 bytes
+            uint2* q = reinterpret_cast<uint2*>(d + (lane - 1) * 24);
+            q[0] = make_uint2(__byte_perm(r0, 0, 0x1000), __byte_perm(r0, 0, 0x2211));
+            q[1] = make_uint2(__byte_perm(r0, 0, 0x3332), __byte_perm(r1, 0, 0x1000));
+            q[2] = make_uint2(__byte_perm(r1, 0, 0x2211), __byte_perm(r1, 0, 0x3332));
+          } else {
+            *reinterpret_cast<uint2*>(d + (lane - 1) * 8) = make_uint2(r0, r1);
+          }
+        }
+        if (er == CH - 1 || t == steps - 1) {  // a box of finished rows leaves by TMA
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&dst_map, xw_out, ya + ec * CH - P.y0, out_ring + ob * P.out_buf_bytes);
+            tma_store_commit();
+          }
+        }
+      }
+      // rotate: what was "row y" becomes "row y-1" for the next gray row
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        accA[i] = accB[i];
+        accB[i] = accC[i];
+        accC[i] = 0;
+      }
+      prev[0] = a[0]; prev[1] = a[1]; prev[2] = a[2]; prev[3] = a[3];
+    }
+    n_in += n_chunks;
+    n_out += (yb - ya + CH - 1) / CH;
+  }
+  if (lane == 0) tma_store_wait_all();
+}
+
+}  // namespace
+
+cudaError_t launch_sweep3(const SweepParams& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
+                          int grid, cudaStream_t stream) {
+  static bool configured[64][4] = {{false}};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const int smem = P.warp_smem * kSweepWarps;
+  const int variant = (P.gray == 1 ? 0 : 2) + (P.has_lut0 ? 1 : 0);
+  auto launch = [&](auto kern) -> cudaError_t {
+    if (dev < 64 && !configured[dev][variant]) {
+      cudaError_t e2 = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      if (e2 != cudaSuccess) return e2;
+      configured[dev][variant] = true;
+    }
+    kern<<<grid, kSweepWarps * 32, smem, stream>>>(P, src_map, dst_map);
+    return cudaGetLastError();
+  };
+  switch (variant) {
+    case 0: return launch(sweep3_kernel<1, false>);
+    case 1: return launch(sweep3_kernel<1, true>);
+    case 2: return launch(sweep3_kernel<2, false>);
+    default: return launch(sweep3_kernel<2, true>);
+  }
+}
+
+}  // namespace b2i

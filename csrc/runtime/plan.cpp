@@ -17,6 +17,7 @@
 #include <vector>
 
 #include "../core/error.hpp"
+#include "../kernels/sweep3.hpp"
 #include "../kernels/tile_plan.hpp"
 
 namespace b2i {
@@ -25,6 +26,8 @@ cudaError_t launch_tile_chain(const TileParams& P, const CUtensorMap& src_map,
                               const CUtensorMap& push_dn_map, int grid, cudaStream_t stream);
 cudaError_t tile_chain_occupancy(int smem_bytes, int* blocks_per_sm);
 cudaError_t launch_pointwise(const PointwiseParams& P, int grid, cudaStream_t stream);
+cudaError_t launch_sweep3(const SweepParams& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
+                          int grid, cudaStream_t stream);
 int run_naive(const b2i_chain_t* chain, const uint8_t* src, int W, int H, int C, size_t src_pitch,
               uint8_t* dst, size_t dst_pitch, uint8_t* tmp0, uint8_t* tmp1, uint8_t* lut_scratch,
               cudaStream_t stream);
@@ -333,12 +336,94 @@ int env_int(const char* name, int dflt) {
   return v && *v ? atoi(v) : dflt;
 }
 
+// The warp-sweep kernel (kernels/sweep3.cu) takes segments of the reference's own shape:
+// gray (+LUT) -> one 3x3 stencil on the gray plane (+LUT, +expand). Returns 1 if it launched,
+// 0 if the segment or the buffers do not qualify (the tile-chain kernel then runs it).
+int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
+              const b2i_view_t& src, const b2i_view_t& dst, int sms) {
+  if (seg.phases.size() != 2 || env_int("B200IMG_NO_SWEEP", 0) || (L.flags & B2I_LAUNCH_NO_TMA) ||
+      env_int("B200IMG_NO_TMA", 0))
+    return 0;
+  const PhaseDesc& g = seg.phases[0];
+  const PhaseDesc& st = seg.phases[1];
+  if ((g.type != PH_GRAY_REF && g.type != PH_GRAY_CV) || st.type != PH_STENCIL || st.ksize != 3 ||
+      st.cin != 1 || seg.cin != 3)
+    return 0;
+  if (L.push_rows || L.wait_up_flag || L.wait_dn_flag || L.signal_up_flag || L.signal_dn_flag || L.done_flag)
+    return 0;
+  if ((L.W & 7) || L.W < 16 || y1 - y0 < 1) return 0;
+  SweepParams P;
+  memset(&P, 0, sizeof P);
+  P.W = L.W;
+  P.H = L.H;
+  P.y0 = y0;
+  P.y1 = y1;
+  P.src_y_begin = src.y_begin;
+  P.gray = g.type == PH_GRAY_REF ? 1 : 2;
+  P.rgb_order = plan->chain.order == B2I_ORDER_RGB;
+  P.has_lut0 = g.lut >= 0;
+  P.has_lut1 = st.lut >= 0;
+  if (g.lut >= 0) memcpy(P.lut0, seg.luts[g.lut], 256);
+  if (st.lut >= 0) memcpy(P.lut1, seg.luts[st.lut], 256);
+  P.border = st.border;
+  P.shift = st.shift;
+  P.bias = st.bias;
+  P.expand = st.expand;
+  for (int k = 0; k < 3; ++k) P.wpk[k] = st.wpk[k][0];
+  const int out_row = st.expand ? kSweepOutBytes : kSweepStrip;
+  P.in_stage_bytes = align_up(kSweepChunk * kSweepInBytes, 128);
+  P.out_buf_bytes = align_up(kSweepChunk * out_row, 128);
+  P.warp_smem = kSweepStages * P.in_stage_bytes + 2 * P.out_buf_bytes;
+  CUtensorMap src_map, dst_map;
+  const int src_rows = std::min(src.y_end, L.H) - src.y_begin;
+  if (!encode_map(&src_map, src.ptr, src.pitch, (int64_t)L.W * 3, src_rows, kSweepInBytes, kSweepChunk)) return 0;
+  const uint64_t dptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
+  if (!encode_map(&dst_map, dptr, dst.pitch, (int64_t)L.W * seg.cout, y1 - y0, out_row, kSweepChunk)) return 0;
+  // segment height: a multiple of the box height, chosen so that the tasks fill the resident
+  // warps evenly and the two halo rows per segment stay cheap
+  P.n_strips = (L.W + kSweepStrip - 1) / kSweepStrip;
+  const int resident = sms * 2 * kSweepWarps;
+  double best = -1;
+  for (int sr = 15; sr <= 96; sr += kSweepChunk) {
+    const long long tasks = (long long)P.n_strips * ((y1 - y0 + sr - 1) / sr);
+    const long long waves = (tasks + resident - 1) / resident;
+    const double eff = (double)tasks / (double)(waves * resident) * sr / (sr + 2.0);
+    if (eff > best + 1e-9) {
+      best = eff;
+      P.seg_rows = sr;
+    }
+  }
+  P.n_tasks = P.n_strips * ((y1 - y0 + P.seg_rows - 1) / P.seg_rows);
+  const int grid = std::max(1, std::min((P.n_tasks + kSweepWarps - 1) / kSweepWarps, sms * 2));
+  plan->info.last_tile_h = -P.seg_rows;  // negative: rows per sweep segment
+  plan->info.last_smem_bytes = P.warp_smem * kSweepWarps;
+  plan->info.last_grid = grid;
+  plan->info.last_blocks_per_sm = 2;
+  plan->info.last_tma_load = plan->info.last_tma_store = 1;
+  plan->info.last_launches++;
+  cudaError_t e = launch_sweep3(P, src_map, dst_map, grid, (cudaStream_t)L.stream);
+  if (e != cudaSuccess) {
+    b2i::fail(B2I_ERR_CUDA, __FILE__, __LINE__, "sweep3 launch: %s", cudaGetErrorString(e));
+    return -1;
+  }
+  return 1;
+}
+
 // One tile-kernel launch: rows [y0,y1) of this segment's result.
 int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
                         const b2i_view_t& src, const b2i_view_t& dst, bool first, bool last) {
   int dev = 0, sms = 0;
   B2I_CUDA(cudaGetDevice(&dev));
   B2I_TRY(device_sms(dev, &sms));
+  {
+    B2I_CHECK_ARG(src.ptr && dst.ptr, "null image view");
+    const int need_a = std::max(0, y0 - seg.halo), need_b = std::min(L.H, y1 + seg.halo);
+    B2I_CHECK_ARG(src.y_begin <= need_a && src.y_end >= need_b && dst.y_begin <= y0 && dst.y_end >= y1,
+                  "views do not cover the band [%d,%d) and its halo", y0, y1);
+    const int sw = try_sweep(plan, seg, L, y0, y1, src, dst, sms);
+    if (sw < 0) return B2I_ERR_CUDA;
+    if (sw > 0) return B2I_OK;
+  }
   TileParams P;
   memset(&P, 0, sizeof P);
   // tile height: tallest that still lets two CTAs share an SM; smaller for small images so that
