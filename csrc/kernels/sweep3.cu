@@ -21,6 +21,8 @@
 #include "device_utils.cuh"
 #include "sweep3.hpp"
 
+#include <type_traits>
+
 namespace b2i {
 using namespace dev;
 
@@ -141,22 +143,29 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
       }
     }
     const bool left_edge = x0 == 0, right_edge = x0 + 8 == P.W, beyond = x0 < 0 || x0 >= P.W;
+    const bool folds = P.border == B2I_BORDER_REFLECT101 || P.border == B2I_BORDER_REPLICATE;
+    const bool edge_fix = folds && (xs == 0 || xs + kSweepStrip >= P.W);         // warp-uniform
+    const bool vert_fix = folds && (ya <= 1 || yb >= P.H - 1);                   // warp-uniform
 
-    int accA[8], accB[8], accC[8];  // output rows y-1, y, y+1 while gray row y is being applied
-    uint32_t prev[4] = {0, 0, 0, 0};                      // window words of the previous gray row
+    // Three accumulator sets, X[j] collecting the output row whose index (relative to ya-1) is
+    // j mod 3. The row loop is unrolled by the box height so that the roles (bottom / middle /
+    // top taps), the input-stage bookkeeping and the store schedule are all static per position.
+    int X0[8], X1[8], X2[8];
+    uint32_t prev[4] = {0, 0, 0, 0};  // window words of the previous gray row
 #pragma unroll
-    for (int i = 0; i < 8; ++i) accA[i] = accB[i] = accC[i] = 0;
+    for (int i = 0; i < 8; ++i) X0[i] = X1[i] = X2[i] = 0;
 
-    for (int t = 0; t < steps; ++t) {
-      const int y = ya - 1 + t;
-      const int c = t / CH, rr = t - c * CH;
-      const uint32_t st = (n_in + c) % NST;
-      if (rr == 0) mbar_wait(&bar[st], ((n_in + c) / NST) & 1);
-      // ---- gray row y: 8 pixels per lane, once -------------------------------------------
+    // one gray row: convert, exchange edge pixels, apply to the three output rows it touches,
+    // emit the output row that is now complete
+    auto step = [&](auto qc, int c, const uint8_t* stage_base, uint32_t ob_prev, uint32_t ob_cur,
+                    int (&A)[8], int (&B)[8], int (&Cc)[8]) {
+      constexpr int q = decltype(qc)::value;
+      const int u = c * CH + q;
+      const int y = ya - 1 + u;
       uint32_t a[4];
       if (y >= 0 && y < P.H) {
         uint32_t g[8];
-        gray8<GRAY>(in_ring + st * P.in_stage_bytes + rr * kSweepInBytes + 8 + lane * 24, gk, rgb, g);
+        gray8<GRAY>(stage_base + q * kSweepInBytes + 8 + lane * 24, gk, rgb, g);
         if (LUT0) {
 #pragma unroll
           for (int i = 0; i < 8; ++i) g[i] = lut0[g[i] & 0xFF];
@@ -169,59 +178,49 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
       }
       a[0] = __shfl_up_sync(0xFFFFFFFFu, a[2], 1);
       a[3] = __shfl_down_sync(0xFFFFFFFFu, a[1], 1);
-      if (P.border == B2I_BORDER_REFLECT101) {  // pixel -1 := pixel 1, pixel W := pixel W-2
-        if (left_edge) a[0] = __byte_perm(a[0], a[1], 0x5210);   // byte 3 <- own byte 1
-        if (right_edge) a[3] = __byte_perm(a[3], a[2], 0x3216);  // byte 0 <- own1 byte 2
-      } else if (P.border == B2I_BORDER_REPLICATE) {
-        if (left_edge) a[0] = __byte_perm(a[0], a[1], 0x4210);   // byte 3 <- own byte 0
-        if (right_edge) a[3] = __byte_perm(a[3], a[2], 0x3217);  // byte 0 <- own1 byte 3
-      }
-      // the stage can be refilled once every lane has read the chunk's last row
-      if (rr == CH - 1 || t == steps - 1) {
-        __syncwarp();
-        if (lane == 0 && c + NST < n_chunks) {
-          mbar_arrive_expect_tx(&bar[st], CH * kSweepInBytes);
-          tma_load_2d(in_ring + st * P.in_stage_bytes, &src_map, xw_in,
-                      ya - 1 + (c + NST) * CH - P.src_y_begin, &bar[st]);
+      if (edge_fix) {
+        if (P.border == B2I_BORDER_REFLECT101) {  // pixel -1 := pixel 1, pixel W := pixel W-2
+          if (left_edge) a[0] = __byte_perm(a[0], a[1], 0x5210);
+          if (right_edge) a[3] = __byte_perm(a[3], a[2], 0x3216);
+        } else {                                  // replicate: pixel -1 := pixel 0, pixel W := pixel W-1
+          if (left_edge) a[0] = __byte_perm(a[0], a[1], 0x4210);
+          if (right_edge) a[3] = __byte_perm(a[3], a[2], 0x3217);
         }
       }
-      // ---- apply gray row y to output rows y-1 (bottom taps), y (middle), y+1 (top) ----------
-      {
-        uint32_t v[8];
-        v[0] = win<3>(a); v[1] = win<4>(a); v[2] = win<5>(a); v[3] = win<6>(a);
-        v[4] = win<7>(a); v[5] = win<8>(a); v[6] = win<9>(a); v[7] = win<10>(a);
-        taps(v, w2, accA);
-        taps(v, w1, accB);
-        taps(v, w0, accC);
-        // vertical borders: row -1 := row 1 / row 0, row H := row H-2 / row H-1
+      uint32_t v[8];
+      v[0] = win<3>(a); v[1] = win<4>(a); v[2] = win<5>(a); v[3] = win<6>(a);
+      v[4] = win<7>(a); v[5] = win<8>(a); v[6] = win<9>(a); v[7] = win<10>(a);
+      taps(v, w2, A);   // bottom taps of output row y-1
+      taps(v, w1, B);   // middle taps of output row y
+      taps(v, w0, Cc);  // top taps of output row y+1
+      if (vert_fix) {   // row -1 := row 1 / row 0, row H := row H-2 / row H-1 (first / last segment only)
         if (P.border == B2I_BORDER_REFLECT101) {
-          if (y == 1) taps(v, w0, accA);                 // row 1 also stands for row -1 (out row 0)
-          if (y == P.H - 1) {                            // row H-2 also stands for row H (out row H-1)
+          if (y == 1) taps(v, w0, A);
+          if (y == P.H - 1) {
             uint32_t pv[8];
             pv[0] = win<3>(prev); pv[1] = win<4>(prev); pv[2] = win<5>(prev); pv[3] = win<6>(prev);
             pv[4] = win<7>(prev); pv[5] = win<8>(prev); pv[6] = win<9>(prev); pv[7] = win<10>(prev);
-            taps(pv, w2, accB);
+            taps(pv, w2, B);
           }
-        } else if (P.border == B2I_BORDER_REPLICATE) {
-          if (y == 0) taps(v, w0, accB);                 // row 0 also stands for row -1
-          if (y == P.H - 1) taps(v, w2, accB);           // row H-1 also stands for row H
+        } else {
+          if (y == 0) taps(v, w0, B);
+          if (y == P.H - 1) taps(v, w2, B);
         }
       }
-      // ---- output row y-1 is complete ---------------------------------------------------------
-      if (t >= 2) {
-        const int e = t - 2;                 // output row index within the task
-        const int ec = e / CH, er = e - ec * CH;
-        const uint32_t ob = (n_out + ec) & 1;
-        if (er == 0) {                       // about to reuse a staging buffer: its store has read it
+      // ---- output row y-1 (index e = u-2 of the task) is complete ----------------------------
+      if (u >= 2) {
+        constexpr int er = (q + 1) % 3;             // row of the store box
+        const uint32_t ob = er == 0 ? ob_cur : ob_prev;
+        if (er == 0) {                               // first row of a box: its previous store has read it
           if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
           __syncwarp();
         }
         if (scale) {
 #pragma unroll
-          for (int i = 0; i < 8; ++i) accA[i] = (accA[i] + P.bias) >> P.shift;
+          for (int i = 0; i < 8; ++i) A[i] = (A[i] + P.bias) >> P.shift;
         }
-        uint32_t r0 = sat_pack4(accA[0], accA[1], accA[2], accA[3]);
-        uint32_t r1 = sat_pack4(accA[4], accA[5], accA[6], accA[7]);
+        uint32_t r0 = sat_pack4(A[0], A[1], A[2], A[3]);
+        uint32_t r1 = sat_pack4(A[4], A[5], A[6], A[7]);
         if (ref) {
           const int oy = y - 1;
           const bool row_ok = oy >= 2 && oy <= P.H - 2;
@@ -236,15 +235,16 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
         if (lane >= 1 && lane <= 30) {
           uint8_t* d = out_ring + ob * P.out_buf_bytes + er * out_pitch;
           if (P.expand) {  // kernel.cu:210 in registers: 8 gray -> 24 bytes
-            uint2* q = reinterpret_cast<uint2*>(d + (lane - 1) * 24);
-            q[0] = make_uint2(__byte_perm(r0, 0, 0x1000), __byte_perm(r0, 0, 0x2211));
-            q[1] = make_uint2(__byte_perm(r0, 0, 0x3332), __byte_perm(r1, 0, 0x1000));
-            q[2] = make_uint2(__byte_perm(r1, 0, 0x2211), __byte_perm(r1, 0, 0x3332));
+            uint2* qd = reinterpret_cast<uint2*>(d + (lane - 1) * 24);
+            qd[0] = make_uint2(__byte_perm(r0, 0, 0x1000), __byte_perm(r0, 0, 0x2211));
+            qd[1] = make_uint2(__byte_perm(r0, 0, 0x3332), __byte_perm(r1, 0, 0x1000));
+            qd[2] = make_uint2(__byte_perm(r1, 0, 0x2211), __byte_perm(r1, 0, 0x3332));
           } else {
             *reinterpret_cast<uint2*>(d + (lane - 1) * 8) = make_uint2(r0, r1);
           }
         }
-        if (er == CH - 1 || t == steps - 1) {  // a box of finished rows leaves by TMA
+        if (er == 2 || u == steps - 1) {  // a box of finished rows leaves by TMA
+          const int ec = (u - 2) / CH;
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
@@ -253,14 +253,28 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
           }
         }
       }
-      // rotate: what was "row y" becomes "row y-1" for the next gray row
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        accA[i] = accB[i];
-        accB[i] = accC[i];
-        accC[i] = 0;
-      }
+      for (int i = 0; i < 8; ++i) A[i] = 0;  // this set collects output row y+2 from the next gray row on
       prev[0] = a[0]; prev[1] = a[1]; prev[2] = a[2]; prev[3] = a[3];
+    };
+
+    for (int c = 0; c < n_chunks; ++c) {
+      const uint32_t st = (n_in + c) % NST;
+      const uint8_t* stage_base = in_ring + st * P.in_stage_bytes;
+      // output box c-1 is finished during rows 0,1 of input box c; box c starts at row 2
+      const uint32_t ob_prev = (n_out + c + 1) & 1, ob_cur = (n_out + c) & 1;
+      const int rows_here = min(CH, steps - c * CH);
+      mbar_wait(&bar[st], ((n_in + c) / NST) & 1);
+      step(std::integral_constant<int, 0>{}, c, stage_base, ob_prev, ob_cur, X2, X0, X1);
+      if (rows_here > 1) step(std::integral_constant<int, 1>{}, c, stage_base, ob_prev, ob_cur, X0, X1, X2);
+      if (rows_here > 2) step(std::integral_constant<int, 2>{}, c, stage_base, ob_prev, ob_cur, X1, X2, X0);
+      // every lane has read the box: the stage can take box c + NST
+      __syncwarp();
+      if (lane == 0 && c + NST < n_chunks) {
+        mbar_arrive_expect_tx(&bar[st], CH * kSweepInBytes);
+        tma_load_2d(in_ring + st * P.in_stage_bytes, &src_map, xw_in, ya - 1 + (c + NST) * CH - P.src_y_begin,
+                    &bar[st]);
+      }
     }
     n_in += n_chunks;
     n_out += (yb - ya + CH - 1) / CH;
