@@ -44,6 +44,10 @@ __device__ __forceinline__ uint32_t win(const uint32_t (&a)[4]) {
   else return __funnelshift_r(a[O >> 2], a[(O >> 2) + 1], (O & 3) * 8);
 }
 
+__device__ __forceinline__ void taps_init(const uint32_t (&v)[8], uint32_t w, int (&acc)[8]) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = dp4a_us(v[i], w, 0);
+}
 // acc[i] += dot(gray[x_i-1 .. x_i+1], w) for the lane's 8 pixels.
 __device__ __forceinline__ void taps(const uint32_t (&v)[8], uint32_t w, int (&acc)[8]) {
 #pragma unroll
@@ -101,6 +105,8 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
   uint8_t* in_ring = smem + warp * P.warp_smem;        // NST stages of CH rows x kSweepInBytes (128 B aligned)
   uint8_t* out_ring = in_ring + NST * P.in_stage_bytes;  // 2 staging buffers of CH rows x out_pitch
   uint64_t* bar = &bars[warp * NST];
+  uint8_t* dummy = out_ring + 2 * P.out_buf_bytes + (lane == 0 ? 0 : 32);  // 64 spare bytes per warp
+  const bool halo_lane = lane == 0 || lane == 31;
   const GrayRefCoef gk = gray_ref_coef(P.rgb_order);
   const int rgb = P.rgb_order;
   const uint32_t w0 = P.wpk[0], w1 = P.wpk[1], w2 = P.wpk[2];
@@ -163,18 +169,18 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
       const int u = c * CH + q;
       const int y = ya - 1 + u;
       uint32_t a[4];
-      if (y >= 0 && y < P.H) {
+      {
+        // branch-free: rows outside the image arrive zero-filled from TMA and are converted like
+        // any other, then replaced by 0 (they contribute nothing; borders are folded in below)
         uint32_t g[8];
         gray8<GRAY>(stage_base + q * kSweepInBytes + 8 + lane * 24, gk, rgb, g);
         if (LUT0) {
 #pragma unroll
           for (int i = 0; i < 8; ++i) g[i] = lut0[g[i] & 0xFF];
         }
-        a[1] = pack4_lo(g[0], g[1], g[2], g[3]);
-        a[2] = pack4_lo(g[4], g[5], g[6], g[7]);
-        if (beyond) a[1] = a[2] = 0;
-      } else {
-        a[1] = a[2] = 0;  // rows outside the image contribute nothing; borders are folded in below
+        const bool valid = (unsigned)y < (unsigned)P.H && !beyond;
+        a[1] = valid ? pack4_lo(g[0], g[1], g[2], g[3]) : 0u;
+        a[2] = valid ? pack4_lo(g[4], g[5], g[6], g[7]) : 0u;
       }
       a[0] = __shfl_up_sync(0xFFFFFFFFu, a[2], 1);
       a[3] = __shfl_down_sync(0xFFFFFFFFu, a[1], 1);
@@ -192,7 +198,7 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
       v[4] = win<7>(a); v[5] = win<8>(a); v[6] = win<9>(a); v[7] = win<10>(a);
       taps(v, w2, A);   // bottom taps of output row y-1
       taps(v, w1, B);   // middle taps of output row y
-      taps(v, w0, Cc);  // top taps of output row y+1
+      taps_init(v, w0, Cc);  // top taps of output row y+1: this set starts here
       if (vert_fix) {   // row -1 := row 1 / row 0, row H := row H-2 / row H-1 (first / last segment only)
         if (P.border == B2I_BORDER_REFLECT101) {
           if (y == 1) taps(v, w0, A);
@@ -232,15 +238,16 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
           r0 = lut4s(lut1, r0);
           r1 = lut4s(lut1, r1);
         }
-        if (lane >= 1 && lane <= 30) {
-          uint8_t* d = out_ring + ob * P.out_buf_bytes + er * out_pitch;
+        {
+          // halo lanes (0, 31) store into a per-warp dummy slot: no divergent branch around the stores
+          uint8_t* d = halo_lane ? dummy : out_ring + ob * P.out_buf_bytes + er * out_pitch + (lane - 1) * (P.expand ? 24 : 8);
           if (P.expand) {  // kernel.cu:210 in registers: 8 gray -> 24 bytes
-            uint2* qd = reinterpret_cast<uint2*>(d + (lane - 1) * 24);
+            uint2* qd = reinterpret_cast<uint2*>(d);
             qd[0] = make_uint2(__byte_perm(r0, 0, 0x1000), __byte_perm(r0, 0, 0x2211));
             qd[1] = make_uint2(__byte_perm(r0, 0, 0x3332), __byte_perm(r1, 0, 0x1000));
             qd[2] = make_uint2(__byte_perm(r1, 0, 0x2211), __byte_perm(r1, 0, 0x3332));
           } else {
-            *reinterpret_cast<uint2*>(d + (lane - 1) * 8) = make_uint2(r0, r1);
+            *reinterpret_cast<uint2*>(d) = make_uint2(r0, r1);
           }
         }
         if (er == 2 || u == steps - 1) {  // a box of finished rows leaves by TMA
@@ -253,8 +260,6 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
           }
         }
       }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) A[i] = 0;  // this set collects output row y+2 from the next gray row on
       prev[0] = a[0]; prev[1] = a[1]; prev[2] = a[2]; prev[3] = a[3];
     };
 

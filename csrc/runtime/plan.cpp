@@ -373,7 +373,7 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
   const int out_row = st.expand ? kSweepOutBytes : kSweepStrip;
   P.in_stage_bytes = align_up(kSweepChunk * kSweepInBytes, 128);
   P.out_buf_bytes = align_up(kSweepChunk * out_row, 128);
-  P.warp_smem = kSweepStages * P.in_stage_bytes + 2 * P.out_buf_bytes;
+  P.warp_smem = kSweepStages * P.in_stage_bytes + 2 * P.out_buf_bytes + 128;  // + dummy slot for the halo lanes
   CUtensorMap src_map, dst_map;
   const int src_rows = std::min(src.y_end, L.H) - src.y_begin;
   if (!encode_map(&src_map, src.ptr, src.pitch, (int64_t)L.W * 3, src_rows, kSweepInBytes, kSweepChunk)) return 0;
