@@ -448,6 +448,27 @@ __device__ void store_tile_generic(const TileParams& P, const Tile& T, const uin
   }
 }
 
+// Thread 0, after tile T's stores (own rows and halo pushes) are complete and fenced: count the
+// tile in; the last tile of each group releases the corresponding flag and re-arms the counter.
+__device__ __forceinline__ void publish_flags(const TileParams& P, const Tile& T, uint32_t* counters,
+                                              int n_push_up, int n_push_dn) {
+  if (P.signal_up_flag && T.ty0 < P.y0 + P.push_rows)
+    if (atomicAdd(&counters[0], 1u) + 1 == (uint32_t)n_push_up) {
+      atomicExch(&counters[0], 0u);
+      st_release_sys(reinterpret_cast<uint32_t*>(P.signal_up_flag), P.signal_epoch);
+    }
+  if (P.signal_dn_flag && T.ty0 + P.th > P.y1 - P.push_rows)
+    if (atomicAdd(&counters[1], 1u) + 1 == (uint32_t)n_push_dn) {
+      atomicExch(&counters[1], 0u);
+      st_release_sys(reinterpret_cast<uint32_t*>(P.signal_dn_flag), P.signal_epoch);
+    }
+  if (P.done_flag)
+    if (atomicAdd(&counters[2], 1u) + 1 == (uint32_t)P.n_tiles) {
+      atomicExch(&counters[2], 0u);
+      st_release_sys(reinterpret_cast<uint32_t*>(P.done_flag), P.signal_epoch);
+    }
+}
+
 }  // namespace
 
 // ---- the kernel -----------------------------------------------------------------------------------
@@ -475,7 +496,12 @@ tile_chain_kernel(const __grid_constant__ TileParams P, const __grid_constant__ 
 
   uint32_t* counters = reinterpret_cast<uint32_t*>(P.counters);
   uint32_t* status = reinterpret_cast<uint32_t*>(P.status);
-  const int push_tile_rows = P.push_rows > 0 ? (P.push_rows + P.th - 1) / P.th : 0;
+  // tiles that take part in a halo push: tile rows starting inside the first push_rows rows
+  // (up), tile rows reaching into the last push_rows rows (down). The last of them to finish
+  // releases the neighbour's flag, so these counts must be exact.
+  const int band_rows = P.y1 - P.y0;
+  const int n_push_up = P.push_rows > 0 ? ((P.push_rows + P.th - 1) / P.th) * P.tiles_x : 0;
+  const int n_push_dn = P.push_rows > 0 ? (P.tiles_y - (band_rows - P.push_rows) / P.th) * P.tiles_x : 0;
 
   // Thread 0: make sure the neighbours' halo rows for this tile have landed in our ghost rows
   // (acquire their flag), then start the TMA load of the tile into stage `s`.
@@ -538,22 +564,7 @@ tile_chain_kernel(const __grid_constant__ TileParams P, const __grid_constant__ 
           if (P.signal_up_flag || P.signal_dn_flag || P.done_flag) {
             asm volatile("fence.proxy.async;" ::: "memory");
             __threadfence_system();
-            const int n_push = push_tile_rows * P.tiles_x;
-            if (P.signal_up_flag && prevT.ty0 < P.y0 + P.push_rows)
-              if (atomicAdd(&counters[0], 1u) + 1 == (uint32_t)n_push) {
-                counters[0] = 0;
-                st_release_sys(reinterpret_cast<uint32_t*>(P.signal_up_flag), P.signal_epoch);
-              }
-            if (P.signal_dn_flag && prevT.ty0 + P.th > P.y1 - P.push_rows)
-              if (atomicAdd(&counters[1], 1u) + 1 == (uint32_t)n_push) {
-                counters[1] = 0;
-                st_release_sys(reinterpret_cast<uint32_t*>(P.signal_dn_flag), P.signal_epoch);
-              }
-            if (P.done_flag)
-              if (atomicAdd(&counters[2], 1u) + 1 == (uint32_t)P.n_tiles) {
-                counters[2] = 0;
-                st_release_sys(reinterpret_cast<uint32_t*>(P.done_flag), P.signal_epoch);
-              }
+            publish_flags(P, prevT, counters, n_push_up, n_push_dn);
           }
         }
         __syncthreads();
@@ -644,22 +655,7 @@ tile_chain_kernel(const __grid_constant__ TileParams P, const __grid_constant__ 
     if (P.signal_up_flag || P.signal_dn_flag || P.done_flag) {
       asm volatile("fence.proxy.async;" ::: "memory");
       __threadfence_system();
-      const int n_push = push_tile_rows * P.tiles_x;
-      if (P.signal_up_flag && prevT.ty0 < P.y0 + P.push_rows)
-        if (atomicAdd(&counters[0], 1u) + 1 == (uint32_t)n_push) {
-          counters[0] = 0;
-          st_release_sys(reinterpret_cast<uint32_t*>(P.signal_up_flag), P.signal_epoch);
-        }
-      if (P.signal_dn_flag && prevT.ty0 + P.th > P.y1 - P.push_rows)
-        if (atomicAdd(&counters[1], 1u) + 1 == (uint32_t)n_push) {
-          counters[1] = 0;
-          st_release_sys(reinterpret_cast<uint32_t*>(P.signal_dn_flag), P.signal_epoch);
-        }
-      if (P.done_flag)
-        if (atomicAdd(&counters[2], 1u) + 1 == (uint32_t)P.n_tiles) {
-          counters[2] = 0;
-          st_release_sys(reinterpret_cast<uint32_t*>(P.done_flag), P.signal_epoch);
-        }
+      publish_flags(P, prevT, counters, n_push_up, n_push_dn);
     }
   }
 }

@@ -125,16 +125,24 @@ extern "C" int b2i_cuda_set_flags(const uint64_t* flags, int n, uint32_t epoch, 
 // cost per step is one kernel launch (the Python/ctypes call overhead would otherwise exceed the
 // kernel time). Step i signals epoch_base+i+1 through the launch's done/signal flags; when
 // n_wait > 0 (the root rank) a flag-wait kernel follows each step, which makes "step i complete"
-// mean "every rank's rows of image i are in the root image".
+// mean "every rank's rows of image i are in the root image". A non-root rank passes the address
+// of its done flag on the root as signal_flag.
 extern "C" int b2i_cuda_run_steps(b2i_plan_t* plan, const b2i_launch_t* launch, int steps,
-                                  uint32_t epoch_base, const uint64_t* wait_flags, int n_wait) {
+                                  uint32_t epoch_base, const uint64_t* wait_flags, int n_wait,
+                                  uint64_t signal_flag) {
   B2I_CHECK_ARG(plan && launch && steps >= 0, "bad arguments");
   b2i_launch_t L = *launch;
   for (int i = 0; i < steps; ++i) {
-    L.signal_epoch = epoch_base + (uint32_t)i + 1;
+    const uint32_t epoch = epoch_base + (uint32_t)i + 1;
+    L.signal_epoch = epoch;
     B2I_TRY(b2i_cuda_run(plan, &L));
-    if (n_wait > 0)
-      B2I_TRY(b2i_cuda_wait_flags(wait_flags, n_wait, L.signal_epoch, L.status, L.timeout_ns, L.stream));
+    // "my rows of image i are in the root image": published by a one-thread kernel that runs
+    // after the filter kernel in stream order (all of its TMA stores have completed by then)
+    if (signal_flag) B2I_TRY(b2i_cuda_set_flags(&signal_flag, 1, epoch, L.stream));
+    if (n_wait > 0) {
+      B2I_CHECK_ARG(L.status, "waiting needs the status word");
+      B2I_TRY(b2i_cuda_wait_flags(wait_flags, n_wait, epoch, L.status, L.timeout_ns, L.stream));
+    }
   }
   return B2I_OK;
 }

@@ -289,9 +289,10 @@ int b2i_cuda_wait_flags(const uint64_t* flags, int n, uint32_t epoch, uint64_t s
                         uint64_t timeout_ns, void* stream);
 int b2i_cuda_set_flags(const uint64_t* flags, int n, uint32_t epoch, void* stream);
 /* K steps of one band launch from C (one kernel launch of host cost per step), epochs rising
- * from epoch_base+1; the root rank passes the other ranks' done flags to wait on each step. */
+ * from epoch_base+1; the root rank passes the other ranks' done flags to wait on each step,
+ * every other rank the address of its own done flag on the root (signal_flag). */
 int b2i_cuda_run_steps(b2i_plan_t* plan, const b2i_launch_t* launch, int steps, uint32_t epoch_base,
-                       const uint64_t* wait_flags, int n_wait);
+                       const uint64_t* wait_flags, int n_wait, uint64_t signal_flag);
 /* `passes` applications of a chain on a resident band, ping-ponging between the two launch
  * descriptions, halo flags waited/signalled with epochs epoch_base+p / epoch_base+p+1. */
 int b2i_cuda_run_resident_steps(b2i_plan_t* plan, const b2i_launch_t* even, const b2i_launch_t* odd,

@@ -161,8 +161,6 @@ class DistRuntime:
         L.dst = View(self.dst.ptrs[self.root], g["dp"], 0, g["H"])    # peer stores = the gather
         L.counters = self.words.local + W_COUNTERS
         L.status = self.words.local + W_STATUS
-        if self.rank != self.root:
-            L.done_flag = self.words.ptrs[self.root] + W_DONE + 4 * self.rank
         L.stream = self.stream()
         L.flags = _lib.LAUNCH_NO_TMA if no_tma else 0
         return L
@@ -177,8 +175,9 @@ class DistRuntime:
                 if r != self.root and band_rows(self.geom["H"], self.world, r)[1] > band_rows(self.geom["H"], self.world, r)[0]:
                     flags[n_wait] = self.words.local + W_DONE + 4 * r
                     n_wait += 1
+        signal = 0 if self.rank == self.root else self.words.ptrs[self.root] + W_DONE + 4 * self.rank
         if self.y1 > self.y0 or n_wait:
-            check(lib.b2i_cuda_run_steps(plan.handle, C.byref(L), steps, self.epoch, flags, n_wait))
+            check(lib.b2i_cuda_run_steps(plan.handle, C.byref(L), steps, self.epoch, flags, n_wait, signal))
         self.epoch += steps
 
     # ---- RESIDENT mode: bands (+ghost rows) stay on their GPUs, kernels push halos ---------------------

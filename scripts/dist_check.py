@@ -45,6 +45,7 @@ def main():
         rt.gather_resident(passes, rt.dst.ptrs[0], rt.geom["dp"], 3)
         got = rt.fetch_root()
         st = rt.status()
+        print(f"   [rank {rank}] {chain} status={st} epoch={rt.epoch}", flush=True)
         if rank == 0:
             want = img
             for _ in range(passes):
