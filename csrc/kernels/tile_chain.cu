@@ -120,7 +120,7 @@ template <int TYPE>
 __device__ void pw_phase(const TileParams& P, const PhaseDesc& ph, uint8_t* sbase, int spitch,
                          int sxorg, int syorg, uint8_t* dbase, int dpitch, int dxorg, int dyorg,
                          const uint8_t* lut) {
-  const int R = P.halo, m = ph.margin, mc = m > 0 ? kMarginCols : 0;
+  const int R = P.halo, m = ph.margin, mc = ph.margin_x > 0 ? kMarginCols : 0;
   const int ux = (kTileW + 2 * mc) >> 2;  // units of 4 pixels per row
   const int rows = P.th + 2 * m;
   const GrayRefCoef gk = gray_ref_coef(P.rgb_order);
@@ -208,7 +208,7 @@ template <int TYPE, bool LUT>
 __device__ void gray_phase(const TileParams& P, const PhaseDesc& ph, const uint8_t* sbase, int spitch,
                            int sxorg, int syorg, uint8_t* dbase, int dpitch, int dxorg, int dyorg,
                            const uint8_t* lut) {
-  const int R = P.halo, m = ph.margin, mc = m > 0 ? kMarginCols : 0;
+  const int R = P.halo, m = ph.margin, mc = ph.margin_x > 0 ? kMarginCols : 0;
   const int ux = (kTileW + 2 * mc) >> 3;  // items of 8 pixels per row: 32 or 34
   const int n = ux * (P.th + 2 * m);
   const GrayRefCoef gk = gray_ref_coef(P.rgb_order);
@@ -293,7 +293,7 @@ __device__ void stencil_phase(const TileParams& P, const PhaseDesc& ph, const Ti
   constexpr int r = K / 2;
   constexpr int RG = SOBEL ? 2 : kRowGroup;
   constexpr int ND = DpCount<C, K>::value;
-  const int R = P.halo, m = ph.margin, mc = m > 0 ? kMarginCols : 0;
+  const int R = P.halo, m = ph.margin, mc = ph.margin_x > 0 ? kMarginCols : 0;
   const int strips = ((kTileW + 2 * mc) * C) >> 3;
   const int rows = P.th + 2 * m;
   const int groups = (rows + RG - 1) / RG;
@@ -402,6 +402,163 @@ __device__ void stencil_phase(const TileParams& P, const PhaseDesc& ph, const Ti
       }
     }
     if (expand) {  // C == 1: 8 gray pixels -> 24 bytes of BGR (kernel.cu:210 fused here)
+      uint8_t* d = dbase + (pr0 - dyorg) * dpitch + (bc - dxorg) * 3;
+#pragma unroll
+      for (int o = 0; o < RG; ++o) {
+        if (o < nvalid) {
+          const uint32_t r0 = res[o][0], r1 = res[o][1];
+          uint2* q = reinterpret_cast<uint2*>(d + o * dpitch);
+          q[0] = make_uint2(__byte_perm(r0, 0, 0x1000), __byte_perm(r0, 0, 0x2211));
+          q[1] = make_uint2(__byte_perm(r0, 0, 0x3332), __byte_perm(r1, 0, 0x1000));
+          q[2] = make_uint2(__byte_perm(r1, 0, 0x2211), __byte_perm(r1, 0, 0x3332));
+        }
+      }
+    } else {
+      uint8_t* d = dbase + (pr0 - dyorg) * dpitch + (bc - dxorg * C);
+#pragma unroll
+      for (int o = 0; o < RG; ++o)
+        if (o < nvalid) *reinterpret_cast<uint2*>(d + o * dpitch) = make_uint2(res[o][0], res[o][1]);
+    }
+  }
+}
+
+// ---- separable stencils (smem -> smem) --------------------------------------------------------------
+// A k x k kernel that factors into a column vector times a row vector (the 5x5 and 3x3 Gaussians)
+// costs 2k taps per byte instead of k*k. The horizontal pass widens bytes to 16-bit lanes
+// (word m of the source -> two words: the even bytes and the odd bytes of word m) and sums the row
+// taps with packed IMADs; the vertical pass sums whole lane words down the rows, rounds, shifts
+// and narrows back to bytes. Exact: lanes never exceed 255 * sum(w) < 65536.
+
+// Bytes [O, O+4) of the 24-byte row window a[0..5].
+template <int O>
+__device__ __forceinline__ uint32_t win24(const uint32_t (&a)[6]) {
+  static_assert(O >= 0 && O <= 20, "window outside the row registers");
+  if constexpr ((O & 3) == 0) return a[O >> 2];
+  else return __funnelshift_r(a[O >> 2], a[(O >> 2) + 1], (O & 3) * 8);
+}
+__device__ __forceinline__ uint32_t even_lanes(uint32_t w) { return __byte_perm(w, 0u, 0x4240); }
+__device__ __forceinline__ uint32_t odd_lanes(uint32_t w) { return __byte_perm(w, 0u, 0x4341); }
+
+// One source word (4 bytes at window offset 8 + 4*WORD) -> its even-lane and odd-lane sums.
+template <int C, int K, int WORD>
+__device__ __forceinline__ void seph_word(const uint32_t (&a)[6], const int (&w)[5], uint32_t& e, uint32_t& o) {
+  constexpr int B = 8 + 4 * WORD;
+  constexpr int r = K / 2;
+  e = 0;
+  o = 0;
+  if constexpr (K == 5) {
+    const uint32_t s0 = win24<B - 2 * C>(a), s4 = win24<B + 2 * C>(a);
+    e = even_lanes(s0) * w[0] + even_lanes(s4) * w[4];
+    o = odd_lanes(s0) * w[0] + odd_lanes(s4) * w[4];
+  }
+  const uint32_t s1 = win24<B - C>(a), s2 = win24<B>(a), s3 = win24<B + C>(a);
+  e += even_lanes(s1) * w[r - 1] + even_lanes(s2) * w[r] + even_lanes(s3) * w[r + 1];
+  o += odd_lanes(s1) * w[r - 1] + odd_lanes(s2) * w[r] + odd_lanes(s3) * w[r + 1];
+}
+
+template <int C, int K>
+__device__ void seph_phase(const TileParams& P, const PhaseDesc& ph, const uint8_t* sbase, int spitch,
+                           uint8_t* dbase, int dpitch) {
+  const int R = P.halo, m = ph.margin, mc = ph.margin_x > 0 ? kMarginCols : 0;
+  const int strips = ((kTileW + 2 * mc) * C) >> 3;
+  const int rows = P.th + 2 * m;
+  int w[5];
+#pragma unroll
+  for (int i = 0; i < 5; ++i) w[i] = ph.sep[i];
+  const int n = strips * rows;
+  int idx = threadIdx.x;
+  const int row0 = idx / strips;
+  int col = idx - row0 * strips;
+  const int drow = kTileThreads / strips, dcol = kTileThreads - drow * strips;
+  const uint8_t* ps = sbase + (R - m + row0) * spitch + (kApron - mc) * C + col * 8 - 8;
+  uint8_t* pd = dbase + (R - m + row0) * dpitch + 2 * ((kApron - mc) * C + col * 8);
+  const int step_s = drow * spitch + dcol * 8, step_d = drow * dpitch + dcol * 16;
+  const int wrap_s = spitch - strips * 8, wrap_d = dpitch - strips * 16;
+  for (; idx < n; idx += kTileThreads) {
+    uint32_t a[6];
+    const uint2 v0 = *reinterpret_cast<const uint2*>(ps), v1 = *reinterpret_cast<const uint2*>(ps + 8),
+                v2 = *reinterpret_cast<const uint2*>(ps + 16);
+    a[0] = v0.x; a[1] = v0.y; a[2] = v1.x; a[3] = v1.y; a[4] = v2.x; a[5] = v2.y;
+    uint4 out;
+    seph_word<C, K, 0>(a, w, out.x, out.y);
+    seph_word<C, K, 1>(a, w, out.z, out.w);
+    *reinterpret_cast<uint4*>(pd) = out;
+    col += dcol;
+    ps += step_s;
+    pd += step_d;
+    if (col >= strips) {
+      col -= strips;
+      ps += wrap_s;
+      pd += wrap_d;
+    }
+  }
+}
+
+// Vertical pass: one thread = an 8-byte strip (four lane words), RG output rows, K + RG - 1 input rows.
+template <int K>
+__device__ void sepv_phase(const TileParams& P, const PhaseDesc& ph, const uint8_t* sbase, int spitch,
+                           uint8_t* dbase, int dpitch, int dxorg, int dyorg, int C, const uint8_t* lut) {
+  constexpr int r = K / 2;
+  constexpr int RG = kRowGroup;
+  const int R = P.halo, m = ph.margin, mc = ph.margin_x > 0 ? kMarginCols : 0;
+  const int strips = ((kTileW + 2 * mc) * C) >> 3;
+  const int rows = P.th + 2 * m;
+  const int groups = (rows + RG - 1) / RG;
+  int w[5];
+#pragma unroll
+  for (int i = 0; i < 5; ++i) w[i] = ph.sep[i];
+  const uint32_t bias2 = (uint32_t)ph.bias * 0x00010001u;
+  const int shift = ph.shift;
+  const bool expand = ph.expand != 0;
+  const int n_items = strips * groups;
+  for (int item = threadIdx.x; item < n_items; item += kTileThreads) {
+    const int g = item / strips, strip = item - g * strips;
+    const int bc = (kApron - mc) * C + strip * 8;
+    const int pr0 = R - m + g * RG;
+    const int nvalid = rows - g * RG;
+    uint32_t acc[RG][4];
+#pragma unroll
+    for (int o = 0; o < RG; ++o)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) acc[o][q] = 0;
+    const uint8_t* srow = sbase + (pr0 - r) * spitch + 2 * bc;
+#pragma unroll
+    for (int j = 0; j < K + RG - 1; ++j) {
+      const uint4 h = *reinterpret_cast<const uint4*>(srow + j * spitch);
+#pragma unroll
+      for (int o = 0; o < RG; ++o) {
+        const int k = j - o;
+        if (k < 0 || k >= K) continue;
+        const uint32_t wk = (uint32_t)w[k];
+        acc[o][0] += h.x * wk;
+        acc[o][1] += h.y * wk;
+        acc[o][2] += h.z * wk;
+        acc[o][3] += h.w * wk;
+      }
+    }
+    uint32_t res[RG][2];
+#pragma unroll
+    for (int o = 0; o < RG; ++o) {
+      // lanes -> bytes: ((lane + bias) >> shift) of the even word gives bytes 0 and 2, odd word 1 and 3
+      uint32_t e0 = acc[o][0] + bias2, o0 = acc[o][1] + bias2, e1 = acc[o][2] + bias2, o1 = acc[o][3] + bias2;
+      if (shift == 8) {
+        res[o][0] = __byte_perm(e0, o0, 0x7351);
+        res[o][1] = __byte_perm(e1, o1, 0x7351);
+      } else {
+        e0 = (e0 >> shift) & 0x00FF00FFu; o0 = (o0 >> shift) & 0x00FF00FFu;
+        e1 = (e1 >> shift) & 0x00FF00FFu; o1 = (o1 >> shift) & 0x00FF00FFu;
+        res[o][0] = e0 | (o0 << 8);
+        res[o][1] = e1 | (o1 << 8);
+      }
+    }
+    if (lut) {
+#pragma unroll
+      for (int o = 0; o < RG; ++o) {
+        res[o][0] = lut4(lut, res[o][0]);
+        res[o][1] = lut4(lut, res[o][1]);
+      }
+    }
+    if (expand) {
       uint8_t* d = dbase + (pr0 - dyorg) * dpitch + (bc - dxorg) * 3;
 #pragma unroll
       for (int o = 0; o < RG; ++o) {
@@ -585,6 +742,19 @@ tile_chain_kernel(const __grid_constant__ TileParams P, const __grid_constant__ 
         case PH_EXPAND:
           pw_phase<PH_EXPAND>(P, ph, sbase, sb.pitch, sb.xorg, sb.yorg, dbase, db.pitch, db.xorg, db.yorg, lut);
           break;
+        case PH_SEPH:
+          if (ph.cin == 1) {
+            if (ph.ksize == 3) seph_phase<1, 3>(P, ph, sbase, sb.pitch, dbase, db.pitch);
+            else seph_phase<1, 5>(P, ph, sbase, sb.pitch, dbase, db.pitch);
+          } else {
+            if (ph.ksize == 3) seph_phase<3, 3>(P, ph, sbase, sb.pitch, dbase, db.pitch);
+            else seph_phase<3, 5>(P, ph, sbase, sb.pitch, dbase, db.pitch);
+          }
+          break;
+        case PH_SEPV:
+          if (ph.ksize == 3) sepv_phase<3>(P, ph, sbase, sb.pitch, dbase, db.pitch, db.xorg, db.yorg, ph.cin, lut);
+          else sepv_phase<5>(P, ph, sbase, sb.pitch, dbase, db.pitch, db.xorg, db.yorg, ph.cin, lut);
+          break;
         case PH_SOBEL:
           if (ph.cin == 1) stencil_phase<1, 3, true>(P, ph, T, sbase, sb.pitch, dbase, db.pitch, db.xorg, db.yorg, lut);
           else stencil_phase<3, 3, true>(P, ph, T, sbase, sb.pitch, dbase, db.pitch, db.xorg, db.yorg, lut);
@@ -602,7 +772,7 @@ tile_chain_kernel(const __grid_constant__ TileParams P, const __grid_constant__ 
       if (ph.dst == BUF_STAGE && P.use_tma_store) fence_proxy_async_smem();
       __syncthreads();
       if (ph.fix_border >= 0 && T.edge) {
-        fix_border(P, T, dbase, db.pitch, ph.cout, ph.margin, ph.fix_border);
+        fix_border(P, T, dbase, db.pitch, ph.cout, max(ph.margin, ph.margin_x), ph.fix_border);
         __syncthreads();
       }
     }

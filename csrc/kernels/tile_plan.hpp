@@ -31,7 +31,9 @@ enum PhaseType : int32_t {
   PH_COPY = 3,      // C -> C, optional LUT
   PH_EXPAND = 4,    // 1 -> 3, optional LUT (kernel.cu:210 when it is not fused into a stencil)
   PH_STENCIL = 5,   // k x k integer correlation (kernel.cu:64-94, kern.cpp:75)
-  PH_SOBEL = 6      // |gx| + |gy|
+  PH_SOBEL = 6,     // |gx| + |gy|
+  PH_SEPH = 7,      // separable stencil, horizontal pass: u8 plane -> plane of 16-bit lanes
+  PH_SEPV = 8       // separable stencil, vertical pass: 16-bit lanes -> u8, rounded and shifted
 };
 
 enum BufId : int32_t { BUF_RAW = 0, BUF_A = 1, BUF_B = 2, BUF_STAGE = 3 };
@@ -40,7 +42,8 @@ struct PhaseDesc {
   int32_t type;
   int32_t cin, cout;      // channels of the input plane / of what is written
   int32_t src, dst;       // BufId
-  int32_t margin;         // rows/pixels around the tile this phase must still produce
+  int32_t margin;         // rows around the tile this phase must still produce
+  int32_t margin_x;       // pixels left/right of the tile this phase must still produce
   int32_t lut;            // LUT slot applied to the phase's result bytes, or -1
   int32_t expand;         // stencil phases: write each result byte three times (gray -> BGR)
   int32_t border;         // b2i_border of this stencil
@@ -50,6 +53,7 @@ struct PhaseDesc {
   int32_t dp_off[3];      // byte offset of each window relative to the output byte
   uint32_t wpk[5][3];     // packed int8 weights, [row][window]
   uint32_t wpk2[3][3];    // Sobel: the gy weights
+  int32_t sep[5];         // PH_SEPH / PH_SEPV: the 1-D weights of this pass
 };
 
 struct BufDesc {

@@ -47,6 +47,8 @@ using namespace b2i;
 
 namespace {
 
+int env_int(const char* name, int dflt);
+
 struct Segment {
   bool pointwise = false;
   int cin = 0, cout = 0, halo = 0;
@@ -96,6 +98,53 @@ void pack_rows(int C, int K, const int* w /*K*K*/, uint32_t out[5][3]) {
       out[j][2] = pack_w(0, 0, 0, r[4]);                 // window at +3: tap +6
     }
   }
+}
+
+// w (k x k, row-major) == outer(wv, wh) with non-negative integers, sum(wv)*sum(wh) == 1<<shift:
+// the kernel can run as two 1-D passes on 16-bit lanes (tile_chain.cu, PH_SEPH / PH_SEPV).
+bool separable(const b2i_op_t& op, int* wv, int* wh) {
+  const int k = op.ksize;
+  if (op.kind != B2I_OP_STENCIL || op.border == B2I_BORDER_REF || op.shift > 8) return false;
+  int j0 = -1, i0 = -1;
+  for (int j = 0; j < k && j0 < 0; ++j)
+    for (int i = 0; i < k; ++i)
+      if (op.weights[j * k + i] != 0) {
+        j0 = j;
+        i0 = i;
+        break;
+      }
+  if (j0 < 0) return false;
+  auto gcd = [](int a, int b) {
+    a = a < 0 ? -a : a;
+    b = b < 0 ? -b : b;
+    while (b) {
+      int t = a % b;
+      a = b;
+      b = t;
+    }
+    return a;
+  };
+  int g = 0;
+  for (int i = 0; i < k; ++i) g = gcd(g, op.weights[j0 * k + i]);
+  if (g == 0) return false;
+  int sv = 0, sh = 0;
+  for (int i = 0; i < k; ++i) {
+    wh[i] = op.weights[j0 * k + i] / g;
+    if (wh[i] < 0) return false;
+    sh += wh[i];
+  }
+  if (wh[i0] == 0) return false;
+  for (int j = 0; j < k; ++j) {
+    if (op.weights[j * k + i0] % wh[i0]) return false;
+    wv[j] = op.weights[j * k + i0] / wh[i0];
+    if (wv[j] < 0) return false;
+    sv += wv[j];
+  }
+  for (int j = 0; j < k; ++j)
+    for (int i = 0; i < k; ++i)
+      if (wv[j] * wh[i] != op.weights[j * k + i]) return false;
+  if (sh > 257 || sv * sh != (1 << op.shift) || op.bias < 0 || op.bias >= (1 << op.shift)) return false;
+  return true;
 }
 
 }  // namespace
@@ -150,7 +199,8 @@ int build_tile_segment(const std::vector<Elem>& el, int cin, Segment& seg) {
         break;
       case B2I_OP_EXPAND:
         if (!seg.phases.empty() &&
-            (seg.phases.back().type == PH_STENCIL || seg.phases.back().type == PH_SOBEL) &&
+            (seg.phases.back().type == PH_STENCIL || seg.phases.back().type == PH_SOBEL ||
+             seg.phases.back().type == PH_SEPV) &&
             !seg.phases.back().expand) {
           seg.phases.back().expand = 1;  // kernel.cu:210 fused into the stencil's store
           seg.phases.back().cout = c = 3;
@@ -161,6 +211,28 @@ int build_tile_segment(const std::vector<Elem>& el, int cin, Segment& seg) {
         break;
       default: {  // stencil / sobel
         const b2i_op_t& op = *e.op;
+        int wv[5] = {0, 0, 0, 0, 0}, wh[5] = {0, 0, 0, 0, 0};
+        if (!env_int("B200IMG_NO_SEP", 0) && separable(op, wv, wh)) {
+          ph.type = PH_SEPH;  // horizontal pass: bytes -> 16-bit lanes
+          ph.cout = c;
+          ph.border = op.border;
+          ph.ksize = op.ksize;
+          for (int q = 0; q < 5; ++q) ph.sep[q] = wh[q];
+          seg.phases.push_back(ph);
+          PhaseDesc pv;
+          memset(&pv, 0, sizeof pv);
+          pv.lut = -1;
+          pv.fix_border = -1;
+          pv.type = PH_SEPV;  // vertical pass: lanes -> bytes, rounded and shifted
+          pv.cin = pv.cout = c;
+          pv.border = op.border;
+          pv.ksize = op.ksize;
+          pv.shift = op.shift;
+          pv.bias = op.bias;
+          for (int q = 0; q < 5; ++q) pv.sep[q] = wv[q];
+          seg.phases.push_back(pv);
+          continue;
+        }
         ph.type = op.kind == B2I_OP_SOBEL ? PH_SOBEL : PH_STENCIL;
         ph.cout = c;
         ph.border = op.border;
@@ -186,13 +258,19 @@ int build_tile_segment(const std::vector<Elem>& el, int cin, Segment& seg) {
   if (seg.phases.empty() || (int)seg.phases.size() > kMaxPhases) return B2I_ERR_UNSUPPORTED;
   seg.cout = c;
   // margins, walking backwards: a phase must produce what the later stencils still consume
-  int margin = 0;
+  int margin = 0, margin_x = 0;
   for (int k = (int)seg.phases.size() - 1; k >= 0; --k) {
     PhaseDesc& ph = seg.phases[k];
     ph.margin = margin;
-    if (ph.type == PH_STENCIL || ph.type == PH_SOBEL) margin += ph.ksize / 2;
+    ph.margin_x = margin_x;
+    if (ph.type == PH_STENCIL || ph.type == PH_SOBEL) {
+      margin += ph.ksize / 2;
+      margin_x += ph.ksize / 2;
+    }
+    if (ph.type == PH_SEPV) margin += ph.ksize / 2;    // the vertical pass widens the rows needed
+    if (ph.type == PH_SEPH) margin_x += ph.ksize / 2;  // the horizontal pass the columns
   }
-  seg.halo = margin;
+  seg.halo = std::max(margin, margin_x);
   if (seg.halo > kMaxSegHalo) return B2I_ERR_UNSUPPORTED;
   // buffers: RAW -> A -> B -> A ... -> STAGE
   seg.chan_a = seg.chan_b = 0;
@@ -202,19 +280,20 @@ int build_tile_segment(const std::vector<Elem>& el, int cin, Segment& seg) {
     ph.src = src;
     const bool last = k + 1 == seg.phases.size();
     ph.dst = last ? BUF_STAGE : (src == BUF_A ? BUF_B : BUF_A);
-    if (ph.dst == BUF_A) seg.chan_a = std::max(seg.chan_a, ph.cout);
-    if (ph.dst == BUF_B) seg.chan_b = std::max(seg.chan_b, ph.cout);
+    const int bpp = ph.type == PH_SEPH ? 2 * ph.cout : ph.cout;  // 16-bit lanes take two bytes per byte
+    if (ph.dst == BUF_A) seg.chan_a = std::max(seg.chan_a, bpp);
+    if (ph.dst == BUF_B) seg.chan_b = std::max(seg.chan_b, bpp);
     src = ph.dst;
     // the border rule a following stencil needs painted onto this phase's result
     if (!last) {
       const PhaseDesc& nx = seg.phases[k + 1];
-      if ((nx.type == PH_STENCIL || nx.type == PH_SOBEL) && nx.border != B2I_BORDER_REF)
+      if ((nx.type == PH_STENCIL || nx.type == PH_SOBEL || nx.type == PH_SEPH) && nx.border != B2I_BORDER_REF)
         ph.fix_border = nx.border;
     }
   }
   const PhaseDesc& p0 = seg.phases[0];
   seg.raw_fix_border = -1;
-  if ((p0.type == PH_STENCIL || p0.type == PH_SOBEL) &&
+  if ((p0.type == PH_STENCIL || p0.type == PH_SOBEL || p0.type == PH_SEPH) &&
       (p0.border == B2I_BORDER_REFLECT101 || p0.border == B2I_BORDER_REPLICATE))
     seg.raw_fix_border = p0.border;  // ZERO is what TMA's out-of-bounds fill already gives
   return B2I_OK;
