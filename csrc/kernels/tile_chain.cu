@@ -209,14 +209,14 @@ __device__ void gray_phase(const TileParams& P, const PhaseDesc& ph, const uint8
                            int sxorg, int syorg, uint8_t* dbase, int dpitch, int dxorg, int dyorg,
                            const uint8_t* lut) {
   const int R = P.halo, m = ph.margin, mc = ph.margin_x > 0 ? kMarginCols : 0;
-  const int ux = (kTileW + 2 * mc) >> 3;  // items of 8 pixels per row: 32 or 34
-  const int n = ux * (P.th + 2 * m);
+  const int ux = ph.units;  // items of 8 pixels per row: 32 or 34
+  const int n = ph.n_items;
   const GrayRefCoef gk = gray_ref_coef(P.rgb_order);
   const int rgb = P.rgb_order;
   int idx = threadIdx.x;
-  const int row0 = idx / ux;
+  const int row0 = (idx * ph.units_magic) >> 20;
   int col = idx - row0 * ux;
-  const int drow = kTileThreads / ux, dcol = kTileThreads - drow * ux;
+  const int drow = ph.drow, dcol = ph.dcol;
   const uint8_t* ps = sbase + (R - m - syorg + row0) * spitch + (kApron - mc - sxorg) * 3 + col * 24;
   uint8_t* pd = dbase + (R - m - dyorg + row0) * dpitch + (kApron - mc - dxorg) + col * 8;
   const int step_s = drow * spitch + dcol * 24, step_d = drow * dpitch + dcol * 8;
@@ -294,9 +294,8 @@ __device__ void stencil_phase(const TileParams& P, const PhaseDesc& ph, const Ti
   constexpr int RG = SOBEL ? 2 : kRowGroup;
   constexpr int ND = DpCount<C, K>::value;
   const int R = P.halo, m = ph.margin, mc = ph.margin_x > 0 ? kMarginCols : 0;
-  const int strips = ((kTileW + 2 * mc) * C) >> 3;
+  const int strips = ph.units;
   const int rows = P.th + 2 * m;
-  const int groups = (rows + RG - 1) / RG;
   const bool ref = ph.border == B2I_BORDER_REF;
   const bool scale = (ph.shift | ph.bias) != 0;
   const bool expand = ph.expand != 0;
@@ -314,9 +313,9 @@ __device__ void stencil_phase(const TileParams& P, const PhaseDesc& ph, const Ti
     }
     if (any || K == 3) rowmask |= 1u << k;
   }
-  const int n_items = strips * groups;
+  const int n_items = ph.n_items;
   for (int item = threadIdx.x; item < n_items; item += kTileThreads) {
-    const int g = item / strips, strip = item - g * strips;
+    const int g = (item * ph.units_magic) >> 20, strip = item - g * strips;
     const int bc = (kApron - mc) * C + strip * 8;  // plane byte column of the strip
     const int pr0 = R - m + g * RG;                 // plane row of the first output row
     const int nvalid = rows - g * RG;               // output rows of this group inside the region
@@ -460,16 +459,15 @@ template <int C, int K>
 __device__ void seph_phase(const TileParams& P, const PhaseDesc& ph, const uint8_t* sbase, int spitch,
                            uint8_t* dbase, int dpitch) {
   const int R = P.halo, m = ph.margin, mc = ph.margin_x > 0 ? kMarginCols : 0;
-  const int strips = ((kTileW + 2 * mc) * C) >> 3;
-  const int rows = P.th + 2 * m;
+  const int strips = ph.units;
   int w[5];
 #pragma unroll
   for (int i = 0; i < 5; ++i) w[i] = ph.sep[i];
-  const int n = strips * rows;
+  const int n = ph.n_items;
   int idx = threadIdx.x;
-  const int row0 = idx / strips;
+  const int row0 = (idx * ph.units_magic) >> 20;
   int col = idx - row0 * strips;
-  const int drow = kTileThreads / strips, dcol = kTileThreads - drow * strips;
+  const int drow = ph.drow, dcol = ph.dcol;
   const uint8_t* ps = sbase + (R - m + row0) * spitch + (kApron - mc) * C + col * 8 - 8;
   uint8_t* pd = dbase + (R - m + row0) * dpitch + 2 * ((kApron - mc) * C + col * 8);
   const int step_s = drow * spitch + dcol * 8, step_d = drow * dpitch + dcol * 16;
@@ -501,18 +499,17 @@ __device__ void sepv_phase(const TileParams& P, const PhaseDesc& ph, const uint8
   constexpr int r = K / 2;
   constexpr int RG = kRowGroup;
   const int R = P.halo, m = ph.margin, mc = ph.margin_x > 0 ? kMarginCols : 0;
-  const int strips = ((kTileW + 2 * mc) * C) >> 3;
+  const int strips = ph.units;
   const int rows = P.th + 2 * m;
-  const int groups = (rows + RG - 1) / RG;
   int w[5];
 #pragma unroll
   for (int i = 0; i < 5; ++i) w[i] = ph.sep[i];
   const uint32_t bias2 = (uint32_t)ph.bias * 0x00010001u;
   const int shift = ph.shift;
   const bool expand = ph.expand != 0;
-  const int n_items = strips * groups;
+  const int n_items = ph.n_items;
   for (int item = threadIdx.x; item < n_items; item += kTileThreads) {
-    const int g = item / strips, strip = item - g * strips;
+    const int g = (item * ph.units_magic) >> 20, strip = item - g * strips;
     const int bc = (kApron - mc) * C + strip * 8;
     const int pr0 = R - m + g * RG;
     const int nvalid = rows - g * RG;

@@ -54,6 +54,9 @@ struct PhaseDesc {
   uint32_t wpk[5][3];     // packed int8 weights, [row][window]
   uint32_t wpk2[3][3];    // Sobel: the gy weights
   int32_t sep[5];         // PH_SEPH / PH_SEPV: the 1-D weights of this pass
+  // filled per launch (they depend on the tile height): work decomposition of the phase, so that
+  // the kernel does no runtime integer division (item / units == (item * units_magic) >> 20)
+  int32_t units, units_magic, n_items, drow, dcol;
 };
 
 struct BufDesc {

@@ -538,7 +538,42 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
   P.rgb_order = plan->chain.order == B2I_ORDER_RGB;
   P.raw_fix_border = seg.raw_fix_border;
   P.debug = env_int("B200IMG_DEBUG", 0);
-  for (int k = 0; k < P.n_phases; ++k) P.ph[k] = seg.phases[k];
+  for (int k = 0; k < P.n_phases; ++k) {
+    PhaseDesc& ph = P.ph[k];
+    ph = seg.phases[k];
+    // work decomposition (see tile_chain.cu): units per row, rows or row groups, items
+    const int mc = ph.margin_x > 0 ? kMarginCols : 0, rows = th + 2 * ph.margin;
+    int units, lines;
+    switch (ph.type) {
+      case PH_GRAY_REF:
+      case PH_GRAY_CV:
+        units = (kTileW + 2 * mc) >> 3;  // 8-pixel items
+        lines = rows;
+        break;
+      case PH_COPY:
+      case PH_EXPAND:
+        units = (kTileW + 2 * mc) >> 2;  // 4-pixel items
+        lines = rows;
+        break;
+      case PH_SEPH:
+        units = ((kTileW + 2 * mc) * ph.cin) >> 3;  // 8-byte strips
+        lines = rows;
+        break;
+      case PH_SOBEL:
+        units = ((kTileW + 2 * mc) * ph.cin) >> 3;
+        lines = (rows + 1) / 2;  // row groups of 2
+        break;
+      default:  // PH_STENCIL, PH_SEPV: 8-byte strips x row groups of kRowGroup
+        units = ((kTileW + 2 * mc) * ph.cin) >> 3;
+        lines = (rows + kRowGroup - 1) / kRowGroup;
+        break;
+    }
+    ph.units = units;
+    ph.units_magic = ((1 << 20) + units - 1) / units;
+    ph.n_items = units * lines;
+    ph.drow = kTileThreads / units;
+    ph.dcol = kTileThreads - ph.drow * units;
+  }
   memcpy(P.luts, seg.luts, sizeof P.luts);
   // views
   B2I_CHECK_ARG(src.ptr && dst.ptr, "null image view");
