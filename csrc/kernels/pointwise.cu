@@ -96,7 +96,10 @@ pointwise_kernel(const __grid_constant__ PointwiseParams P) {
         const uint4 v = ldg_stream_v4(s + 16 * q);
         in[4 * q] = v.x; in[4 * q + 1] = v.y; in[4 * q + 2] = v.z; in[4 * q + 3] = v.w;
       }
-      if (P.has_lut0) {
+      if (P.has_lut0 == 2) {  // the table is 255 - v (invert): one NOT per word instead of four lookups
+#pragma unroll
+        for (int q = 0; q < 4 * CIN; ++q) in[q] = ~in[q];
+      } else if (P.has_lut0) {
 #pragma unroll
         for (int q = 0; q < 4 * CIN; ++q) in[q] = lut4(lut0, in[q]);
       }
@@ -108,7 +111,10 @@ pointwise_kernel(const __grid_constant__ PointwiseParams P) {
 #pragma unroll
         for (int q = 0; q < 4 * MID; ++q) mid[q] = in[q];
       }
-      if (P.has_lut1) {
+      if (P.has_lut1 == 2) {
+#pragma unroll
+        for (int q = 0; q < 4 * MID; ++q) mid[q] = ~mid[q];
+      } else if (P.has_lut1) {
 #pragma unroll
         for (int q = 0; q < 4 * MID; ++q) mid[q] = lut4(lut1, mid[q]);
       }

@@ -702,8 +702,17 @@ int launch_pointwise_segment(b2i_plan* plan, const Segment& seg, const b2i_launc
   P.gray = seg.pw_gray;
   P.expand = seg.pw_expand;
   P.rgb_order = plan->chain.order == B2I_ORDER_RGB;
-  P.has_lut0 = seg.pw_has_lut0;
-  P.has_lut1 = seg.pw_has_lut1;
+  auto lut_kind = [](int has, const uint8_t* lut) {  // 0 none, 1 table, 2 the table is 255 - v
+    if (!has) return 0;
+    bool ident = true, inv = true;
+    for (int v = 0; v < 256; ++v) {
+      ident = ident && lut[v] == v;
+      inv = inv && lut[v] == 255 - v;
+    }
+    return ident ? 0 : inv ? 2 : 1;
+  };
+  P.has_lut0 = lut_kind(seg.pw_has_lut0, seg.pw_lut0);
+  P.has_lut1 = lut_kind(seg.pw_has_lut1, seg.pw_lut1);
   memcpy(P.lut0, seg.pw_lut0, 256);
   memcpy(P.lut1, seg.pw_lut1, 256);
   P.src_pitch = src.pitch;
