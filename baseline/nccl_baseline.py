@@ -45,7 +45,8 @@ def main():
     assert H % world == 0, "the baseline scatters equal bands (like kernel.cu:117 it cannot take a remainder)"
     hb = H // world
     plan = Plan(a.chain, 3)
-    halo, oc = plan.halo, plan.cout
+    # one row more than the chain's halo: the REF border rule leaves r+1 rows at a sub-image's edge unfiltered
+    halo, oc = plan.halo + 1, plan.cout
     assert a.passes == 1 or oc == 3
     img = b2.synth_image(W, H, 3, seed=1) if rank == 0 else None
     full = torch.from_numpy(img).to(dev) if rank == 0 else None
