@@ -141,3 +141,22 @@ def test_output_into_preallocated_tensor_and_stream():
     s.synchronize()
     assert r.data_ptr() == out.data_ptr()
     assert np.array_equal(out.cpu().numpy(), b2.host_run("kernel_cu", img))
+
+
+def test_batch_streamer_frames_from_pinned_memory():
+    from mpi_cuda_imagemanipulation_b200.parallel.batch import BatchStreamer
+    frames = [torch.from_numpy(b2.synth_image(640, 360, 3, seed=s)).pin_memory() for s in range(7)]
+    outs = [torch.empty((360, 640, 1), dtype=torch.uint8).pin_memory() for _ in range(7)]
+    n = BatchStreamer("gray,gauss5", gpus=torch.cuda.device_count()).run(frames, outs)
+    assert n == 7
+    for f, o in zip(frames, outs):
+        assert np.array_equal(o.numpy(), b2.host_run("gray,gauss5", f.numpy()))
+
+
+def test_pipeline_public_api_on_host_and_device_images():
+    img = b2.synth_image(800, 300, 3, seed=3)
+    want = b2.host_run("kernel_cu", img)
+    pipe = b2.kernel_cu()
+    assert np.array_equal(pipe(img), want)                                  # numpy in, numpy out
+    assert np.array_equal(pipe(torch.from_numpy(img).cuda()).cpu().numpy(), want)   # CUDA tensor, zero-copy
+    assert np.array_equal(b2.kern_cpp()(img), b2.host_run("kern_cpp", img))
