@@ -66,35 +66,61 @@ __device__ __forceinline__ void scalar_px(const PointwiseParams& P, const uint8_
   }
 }
 
+// One warp moves 512 pixels per step. Every global access is a fully coalesced 16-byte-per-lane
+// instruction (lane l touches bytes [16 l, 16 l + 16) of a 512-byte run); where a lane needs its
+// own 16 pixels as 48 contiguous bytes (3-channel in or out) the warp transposes through 1536
+// bytes of shared memory (both access patterns are bank-conflict free). The first version let
+// each lane load its 48 bytes directly: three instructions with a 48-byte lane stride, each
+// fetching every sector of the run again (L1 allocation is off for streaming data), which capped
+// `invert` at 0.64 of the HBM roofline.
 template <int CIN, int GRAY, bool EXPAND>
 __global__ void __launch_bounds__(kPwThreads)
 pointwise_kernel(const __grid_constant__ PointwiseParams P) {
   __shared__ __align__(16) uint8_t lut0[256];
   __shared__ __align__(16) uint8_t lut1[256];
+  __shared__ __align__(16) uint8_t xpose[kPwThreads / 32][1536];
   for (int i = threadIdx.x; i < 64; i += kPwThreads) {
     reinterpret_cast<uint32_t*>(lut0)[i] = reinterpret_cast<const uint32_t*>(P.lut0)[i];
     reinterpret_cast<uint32_t*>(lut1)[i] = reinterpret_cast<const uint32_t*>(P.lut1)[i];
   }
   __syncthreads();
   constexpr int COUT = GRAY ? (EXPAND ? 3 : 1) : (EXPAND ? 3 : CIN);
-  constexpr int MID = GRAY ? 1 : CIN;  // channels between the two LUTs
+  constexpr int MID = GRAY ? 1 : CIN;          // channels between the two LUTs
+  constexpr bool BYTEWISE = !GRAY && !EXPAND;  // C -> C per byte: no pixel structure needed
   const GrayRefCoef gk = gray_ref_coef(P.rgb_order);
-  const int units_x = (P.W + 15) >> 4;  // 16 pixels per unit
-  const long long n_units = (long long)units_x * P.rows;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint8_t* xp = xpose[warp];
+  const int su_x = (P.W + 511) >> 9;  // 512-pixel super-units per row
+  const long long n_su = (long long)su_x * P.rows;
+  const long long warps_total = (long long)gridDim.x * (kPwThreads / 32);
   const uint8_t* src = reinterpret_cast<const uint8_t*>(P.src_ptr);
   uint8_t* dst = reinterpret_cast<uint8_t*>(P.dst_ptr);
-  for (long long u = (long long)blockIdx.x * kPwThreads + threadIdx.x; u < n_units;
-       u += (long long)gridDim.x * kPwThreads) {
-    const int y = (int)(u / units_x), ux = (int)(u - (long long)y * units_x);
-    const int x0 = ux << 4;
-    const uint8_t* s = src + (long long)y * P.src_pitch + (long long)x0 * CIN;
-    uint8_t* d = dst + (long long)y * P.dst_pitch + (long long)x0 * COUT;
-    if (P.vec_ok && x0 + 16 <= P.W) {
+  for (long long u = (long long)blockIdx.x * (kPwThreads / 32) + warp; u < n_su; u += warps_total) {
+    const int y = (int)(u / su_x), sx = (int)(u - (long long)y * su_x);
+    const int xw = sx << 9;  // first pixel of the warp's run
+    const uint8_t* srow = src + (long long)y * P.src_pitch + (long long)xw * CIN;
+    uint8_t* drow = dst + (long long)y * P.dst_pitch + (long long)xw * COUT;
+    if (P.vec_ok && xw + 512 <= P.W) {
       uint32_t in[4 * CIN];
+      if (BYTEWISE || CIN == 1) {
+        // bytes are independent (or one byte is one pixel): keep the coalesced layout
 #pragma unroll
-      for (int q = 0; q < CIN; ++q) {
-        const uint4 v = ldg_stream_v4(s + 16 * q);
-        in[4 * q] = v.x; in[4 * q + 1] = v.y; in[4 * q + 2] = v.z; in[4 * q + 3] = v.w;
+        for (int q = 0; q < CIN; ++q) {
+          const uint4 v = ldg_stream_v4(srow + q * 512 + lane * 16);
+          in[4 * q] = v.x; in[4 * q + 1] = v.y; in[4 * q + 2] = v.z; in[4 * q + 3] = v.w;
+        }
+      } else {
+        // 3-channel pixels: coalesced loads, then each lane picks up its own 48 contiguous bytes
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+          *reinterpret_cast<uint4*>(xp + q * 512 + lane * 16) = ldg_stream_v4(srow + q * 512 + lane * 16);
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+          const uint4 v = *reinterpret_cast<const uint4*>(xp + lane * 48 + q * 16);
+          in[4 * q] = v.x; in[4 * q + 1] = v.y; in[4 * q + 2] = v.z; in[4 * q + 3] = v.w;
+        }
+        __syncwarp();
       }
       if (P.has_lut0 == 2) {  // the table is 255 - v (invert): one NOT per word instead of four lookups
 #pragma unroll
@@ -118,7 +144,7 @@ pointwise_kernel(const __grid_constant__ PointwiseParams P) {
 #pragma unroll
         for (int q = 0; q < 4 * MID; ++q) mid[q] = lut4(lut1, mid[q]);
       }
-      if (EXPAND) {  // MID == 1: 16 gray bytes -> 48 bytes
+      if (EXPAND) {  // MID == 1: the lane's 16 gray bytes -> 48 bytes, transposed back to coalesced stores
         uint32_t e[12];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
@@ -127,17 +153,23 @@ pointwise_kernel(const __grid_constant__ PointwiseParams P) {
           e[3 * q + 2] = __byte_perm(mid[q], 0, 0x3332);
         }
 #pragma unroll
+        for (int q = 0; q < 3; ++q)  // 16-byte stores at a 48-byte lane stride: conflict free
+          *reinterpret_cast<uint4*>(xp + lane * 48 + q * 16) = make_uint4(e[4 * q], e[4 * q + 1], e[4 * q + 2], e[4 * q + 3]);
+        __syncwarp();
+#pragma unroll
         for (int q = 0; q < 3; ++q)
-          stg_stream_v4(d + 16 * q, make_uint4(e[4 * q], e[4 * q + 1], e[4 * q + 2], e[4 * q + 3]));
+          stg_stream_v4(drow + q * 512 + lane * 16, *reinterpret_cast<const uint4*>(xp + q * 512 + lane * 16));
+        __syncwarp();
       } else {
 #pragma unroll
         for (int q = 0; q < MID; ++q)
-          stg_stream_v4(d + 16 * q, make_uint4(mid[4 * q], mid[4 * q + 1], mid[4 * q + 2], mid[4 * q + 3]));
+          stg_stream_v4(drow + q * 512 + lane * 16, make_uint4(mid[4 * q], mid[4 * q + 1], mid[4 * q + 2], mid[4 * q + 3]));
       }
     } else {
-      const int n = min(16, P.W - x0);
-      for (int i = 0; i < n; ++i)
-        scalar_px<CIN, GRAY, EXPAND>(P, s + i * CIN, d + i * COUT, lut0, lut1);
+      // ragged end of a row, or buffers that are not 16-byte aligned: one pixel at a time
+      const int n = min(512, P.W - xw);
+      for (int i = lane; i < n; i += 32)
+        scalar_px<CIN, GRAY, EXPAND>(P, srow + i * CIN, drow + i * COUT, lut0, lut1);
     }
   }
   // gather completion: the last CTA to finish releases the root's flag
@@ -147,7 +179,7 @@ pointwise_kernel(const __grid_constant__ PointwiseParams P) {
     if (threadIdx.x == 0) {
       uint32_t* counters = reinterpret_cast<uint32_t*>(P.counters);
       if (atomicAdd(&counters[3], 1u) + 1 == gridDim.x) {
-        counters[3] = 0;
+        atomicExch(&counters[3], 0u);
         __threadfence_system();
         st_release_sys(reinterpret_cast<uint32_t*>(P.done_flag), P.signal_epoch);
       }

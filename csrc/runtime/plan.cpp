@@ -727,8 +727,8 @@ int launch_pointwise_segment(b2i_plan* plan, const Segment& seg, const b2i_launc
     P.counters = L.counters;
     P.signal_epoch = L.signal_epoch;
   }
-  const long long units = (long long)((L.W + 15) / 16) * P.rows;
-  const long long want = (units + 255) / 256;
+  const long long units = (long long)((L.W + 511) / 512) * P.rows;  // one warp per 512-pixel run
+  const long long want = (units + 7) / 8;
   const int grid = (int)std::max(1LL, std::min(want, (long long)sms * 8));
   plan->info.last_grid = grid;
   plan->info.last_tile_h = 0;
