@@ -10,6 +10,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <dirent.h>
+
+#include <algorithm>
 #include <string>
 #include <vector>
 
@@ -19,7 +22,7 @@ namespace {
 
 struct Options {
   std::string input, output = "imageFinalEmboss2.ppm", format, filters, preset, border,
-              backend = "auto", order = "bgr", synth;
+              backend = "auto", order = "bgr", synth, batch, outdir = ".";
   int width = 0, height = 0, channels = 3, gpus = 1, ranks = 0, root = 0, iters = 1;
   bool json = false, verbose = false, seams = false, topology = false, no_tma = false,
        naive = false, help = false, resident = false;
@@ -34,6 +37,7 @@ void usage() {
       "  --format ppm|pgm|raw file format (default: by extension)\n"
       "  --width W --height H --channels C   geometry of raw input\n"
       "  --synth WxH          use a synthetic WxH test card as input\n"
+      "  --batch DIR          filter every .ppm/.pgm in DIR (one after the other) into --outdir\n"
       "  --order bgr|rgb      channel order in memory (default bgr, like cv::imread)\n"
       "  --filters SPEC       e.g. gray,contrast:3.5,emboss3  (see include/b200img.h)\n"
       "  --preset NAME        kernel_cu (default) | kernel_cu_5x5 | kern_cpp\n"
@@ -80,6 +84,8 @@ int main(int argc, char** argv) {
     else if (a == "--height") o.height = atoi(next("--height"));
     else if (a == "--channels") o.channels = atoi(next("--channels"));
     else if (a == "--synth") o.synth = next("--synth");
+    else if (a == "--batch") o.batch = next("--batch");
+    else if (a == "--outdir") o.outdir = next("--outdir");
     else if (a == "--order") o.order = next("--order");
     else if (a == "--filters" || a == "-f") o.filters = next("--filters");
     else if (a == "--preset") o.preset = next("--preset");
@@ -127,6 +133,53 @@ int main(int argc, char** argv) {
   } else {
     if (b2i_chain_preset(o.preset.empty() ? "kernel_cu" : o.preset.c_str(), order, &chain) != B2I_OK)
       return fail("--preset");
+  }
+
+  // ---- batch: every image of a directory through the same chain (the reference handles exactly
+  // one hard-coded image per process launch) ---------------------------------------------------
+  if (!o.batch.empty()) {
+    std::vector<std::string> files;
+    if (DIR* d = opendir(o.batch.c_str())) {
+      while (dirent* e = readdir(d)) {
+        const std::string n = e->d_name;
+        if (ends_with(n, ".ppm") || ends_with(n, ".pgm")) files.push_back(n);
+      }
+      closedir(d);
+    } else {
+      fprintf(stderr, "b200img: cannot open directory '%s'\n", o.batch.c_str());
+      return 1;
+    }
+    std::sort(files.begin(), files.end());
+    std::string backend = o.backend == "auto" ? (b2i_cuda_device_count() > 0 ? "cuda" : "host") : o.backend;
+    double total = 0;
+    int done = 0;
+    for (const std::string& f : files) {
+      uint8_t* im = nullptr;
+      int w = 0, h = 0, c = 0;
+      if (b2i_read_pnm((o.batch + "/" + f).c_str(), order, &im, &w, &h, &c) != B2I_OK) return fail(f.c_str());
+      const int oc = b2i_chain_out_channels(&chain, c);
+      if (oc < 0) return fail("chain");
+      std::vector<uint8_t> res((size_t)w * h * oc);
+      double ms = 0, tot = 0;
+      int rc;
+      if (backend == "host")
+        rc = b2i_host_run_ranks(&chain, im, w, h, c, (size_t)w * c, res.data(), (size_t)w * oc,
+                                o.ranks > 0 ? o.ranks : o.gpus, o.seams, &ms);
+      else
+        rc = b2i_cuda_run_host_image(&chain, im, w, h, c, (size_t)w * c, res.data(), (size_t)w * oc, done % std::max(1, o.gpus),
+                                     1, o.no_tma ? B2I_LAUNCH_NO_TMA : 0, &ms, &tot);
+      b2i_free(im);
+      if (rc != B2I_OK) return fail(f.c_str());
+      std::string outp = o.outdir + "/" + f;
+      if (oc == 1 && ends_with(outp, ".ppm")) outp.replace(outp.size() - 3, 3, "pgm");
+      if (oc == 3 && ends_with(outp, ".pgm")) outp.replace(outp.size() - 3, 3, "ppm");
+      if (b2i_write_pnm(outp.c_str(), order, res.data(), w, h, oc, (size_t)w * oc) != B2I_OK) return fail("write");
+      total += ms;
+      ++done;
+    }
+    printf("{\"batch\": \"%s\", \"frames\": %d, \"backend\": \"%s\", \"filter_ms_total\": %.4f}\n", o.batch.c_str(), done,
+           backend.c_str(), total);
+    return 0;
   }
 
   // ---- input: rank-0-only load in the reference (kernel.cu:109-119) ------------------------

@@ -83,3 +83,19 @@ def test_cuda_backend_single_and_multi_band(tmp_path):
         assert np.array_equal(b2.read_image(str(tmp_path / "o.ppm")), want), extra
     r = subprocess.run([_exe(), "--topology"], capture_output=True, text=True)
     assert r.returncode == 0 and len(json.loads(r.stdout)["devices"]) >= 1
+
+
+def test_batch_directory(tmp_path):
+    (tmp_path / "in").mkdir()
+    (tmp_path / "out").mkdir()
+    imgs = {}
+    for i in range(3):
+        imgs[f"f{i}.ppm"] = b2.synth_image(64 + 16 * i, 40, 3, seed=i)
+        b2.write_image(str(tmp_path / "in" / f"f{i}.ppm"), imgs[f"f{i}.ppm"])
+    r = subprocess.run([_exe(), "--batch", "in", "--outdir", "out", "--filters", "gray,gauss5", "--backend", "host"],
+                       cwd=tmp_path, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert json.loads(r.stdout)["frames"] == 3
+    for name, img in imgs.items():
+        got = b2.read_image(str(tmp_path / "out" / name.replace(".ppm", ".pgm")))
+        assert np.array_equal(got, b2.host_run("gray,gauss5", img))
