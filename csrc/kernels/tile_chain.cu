@@ -602,6 +602,15 @@ __device__ void store_tile_generic(const TileParams& P, const Tile& T, const uin
   }
 }
 
+// Does tile T take part in a flag this launch publishes? Only those tiles pay for the full
+// store completion, the proxy fence and the system-scope fence; all other tiles just wait until
+// their TMA store has read the staging buffer. (The first version fenced after every tile: a
+// membar.sys per tile on thread 0 cost ~35 us per pass at N = 2.)
+__device__ __forceinline__ bool tile_publishes(const TileParams& P, const Tile& T) {
+  return P.done_flag != 0 || (P.signal_up_flag && T.ty0 < P.y0 + P.push_rows) ||
+         (P.signal_dn_flag && T.ty0 + P.th > P.y1 - P.push_rows);
+}
+
 // Thread 0, after tile T's stores (own rows and halo pushes) are complete and fenced: count the
 // tile in; the last tile of each group releases the corresponding flag and re-arms the counter.
 __device__ __forceinline__ void publish_flags(const TileParams& P, const Tile& T, uint32_t* counters,
@@ -714,11 +723,13 @@ tile_chain_kernel(const __grid_constant__ TileParams P, const __grid_constant__ 
         // the previous tile's TMA store must have drained the staging tile before it is reused;
         // waiting for full completion here also lets thread 0 publish that tile's flags
         if (tid == 0) {
-          tma_store_wait_all();
-          if (P.signal_up_flag || P.signal_dn_flag || P.done_flag) {
+          if (tile_publishes(P, prevT)) {
+            tma_store_wait_all();
             asm volatile("fence.proxy.async;" ::: "memory");
             __threadfence_system();
             publish_flags(P, prevT, counters, n_push_up, n_push_dn);
+          } else {
+            tma_store_wait_read();
           }
         }
         __syncthreads();
@@ -808,7 +819,7 @@ tile_chain_kernel(const __grid_constant__ TileParams P, const __grid_constant__ 
         store_tile_generic(P, T, stage, P.push_dn_ptr, P.push_pitch, P.push_dn_y_begin,
                            P.y1 - P.push_rows, P.y1);
     }
-    if (!P.use_tma_store && (P.signal_up_flag || P.signal_dn_flag || P.done_flag))
+    if (!P.use_tma_store && tile_publishes(P, T))
       __threadfence_system();  // plain stores: make them visible before thread 0 publishes flags
     store_pending = true;
     prevT = T;
@@ -819,7 +830,7 @@ tile_chain_kernel(const __grid_constant__ TileParams P, const __grid_constant__ 
   // drain: the last tile's stores, then its flags
   if (tid == 0 && store_pending) {
     if (P.use_tma_store) tma_store_wait_all();
-    if (P.signal_up_flag || P.signal_dn_flag || P.done_flag) {
+    if (tile_publishes(P, prevT)) {
       asm volatile("fence.proxy.async;" ::: "memory");
       __threadfence_system();
       publish_flags(P, prevT, counters, n_push_up, n_push_dn);

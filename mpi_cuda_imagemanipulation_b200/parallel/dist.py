@@ -132,7 +132,25 @@ class DistRuntime:
         self.geom = dict(W=W, H=H, C=Cn, out_c=out_c, sp=sp, dp=dp)
         self.src = self.symmetric(sp * H)      # only the root's copy is used
         self.dst = self.symmetric(dp * H)
-        self.y0, self.y1 = band_rows(H, self.world, self.rank)
+        self.set_root_share(None)
+
+    def set_root_share(self, share):
+        """Band plan of ROOT mode. share=None: equal bands (the reference's plan, kernel.cu:117, with
+        the remainder kept). share=f in (0,1): the root GPU takes the first f*H rows, the other
+        ranks split the rest evenly. The root reads and writes its own HBM while every other rank
+        moves its band through the root's one NVLink port, so equal bands leave the root idle
+        most of the step; :meth:`calibrate_root` measures both rates and picks f."""
+        H = self.geom["H"]
+        if share is None or self.world == 1:
+            self.bands = [band_rows(H, self.world, r) for r in range(self.world)]
+        else:
+            cut = min(H, max(0, int(round(H * share))))
+            self.bands = [(0, cut)] + [tuple(cut + b for b in band_rows(H - cut, self.world - 1, r))
+                                       for r in range(self.world - 1)]
+            if self.root != 0:
+                raise NotImplementedError("weighted bands assume root 0")
+        self.root_share = share
+        self.y0, self.y1 = self.bands[self.rank]
 
     def load_root(self, img: np.ndarray):
         g = self.geom
@@ -172,7 +190,7 @@ class DistRuntime:
         n_wait, flags = 0, (C.c_uint64 * _lib.B2I_MAX_GPUS)()
         if self.rank == self.root:
             for r in range(self.world):
-                if r != self.root and band_rows(self.geom["H"], self.world, r)[1] > band_rows(self.geom["H"], self.world, r)[0]:
+                if r != self.root and self.bands[r][1] > self.bands[r][0]:
                     flags[n_wait] = self.words.local + W_DONE + 4 * r
                     n_wait += 1
         signal = 0 if self.rank == self.root else self.words.ptrs[self.root] + W_DONE + 4 * self.rank
@@ -180,13 +198,45 @@ class DistRuntime:
             check(lib.b2i_cuda_run_steps(plan.handle, C.byref(L), steps, self.epoch, flags, n_wait, signal))
         self.epoch += steps
 
+    def calibrate_root(self, plan, steps: int = 8) -> float:
+        """Measures the root's local rate and the other ranks' combined (link-bound) rate with equal
+        bands, then sets the root's share so that both finish together. Collective."""
+        if self.world == 1:
+            return 1.0
+        self.set_root_share(None)
+        self.run_root(plan, 3)
+        self.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        # every rank times only its own band kernels (no waiting for the others)
+        L = self._root_launch()
+        dist.barrier()
+        e0.record()
+        for _ in range(steps):
+            check(lib.b2i_cuda_run(plan.handle, C.byref(L)))
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        rows = self.y1 - self.y0
+        t = torch.tensor([ms if self.rank == self.root else 0.0, 0.0 if self.rank == self.root else ms,
+                          float(rows if self.rank == self.root else 0), float(0 if self.rank == self.root else rows)],
+                         device=self.device, dtype=torch.float64)
+        tmax = t.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)      # times: root's, slowest remote's
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)         # rows: root's, all remotes'
+        r_root = t[2].item() / max(tmax[0].item(), 1e-6)
+        r_rem = t[3].item() / max(tmax[1].item(), 1e-6)  # remotes run concurrently on one shared link
+        share = r_root / (r_root + r_rem)
+        self.set_root_share(share)
+        self.barrier()
+        return share
+
     # ---- RESIDENT mode: bands (+ghost rows) stay on their GPUs, kernels push halos ---------------------
     def setup_resident(self, W: int, H: int, Cn: int):
         bp = (W * 3 + 15) // 16 * 16
         rows = max(band_rows(H, self.world, r)[1] - band_rows(H, self.world, r)[0] for r in range(self.world))
         self.rgeom = dict(W=W, H=H, C=Cn, bp=bp)
         self.band = [self.symmetric(bp * (rows + 2 * G)), self.symmetric(bp * (rows + 2 * G))]
-        self.y0, self.y1 = band_rows(H, self.world, self.rank)
+        self.y0, self.y1 = band_rows(H, self.world, self.rank)   # resident bands are equal: no root link involved
 
     def scatter_resident(self, src_ptr_on_root: int, src_pitch: int):
         """Band + ghost rows from the root image into buffer 0 (a peer read, once)."""
@@ -268,6 +318,11 @@ def bench_distributed(args, rank: int, world: int, local: int) -> Optional[dict]
     img = b2.synth_image(W, H, 3, seed=1) if rank == 0 else None
     rt.setup_root(W, H, 3, 3)
     rt.load_root(img)
+    # equal bands first (the reference's plan), for the record; then bands sized to the link
+    rt.run_root(plan, Wm)
+    rt.barrier()
+    ms_equal = statistics.median([_timed(lambda: rt.run_root(plan, K)) / K for _ in range(3)])
+    share = rt.calibrate_root(plan)
     rt.run_root(plan, Wm)
     rt.barrier()
     got = rt.fetch_root()
@@ -275,7 +330,7 @@ def bench_distributed(args, rank: int, world: int, local: int) -> Optional[dict]
         rows = (0, 64)
         want = b2.host_run(chain, img, rows=rows)
         assert (got[rows[0]:rows[1]] == want).all(), "bench output mismatch (top rows)"
-        y = (H // world) - 8 if world > 1 else H // 2      # across the first band boundary
+        y = max(0, min(H - 16, rt.bands[0][1] - 8))          # across the first band boundary
         want = b2.host_run(chain, img, rows=(y, y + 16))
         assert (got[y:y + 16] == want).all(), "bench output mismatch (band boundary)"
     info = plan.info()
@@ -292,6 +347,7 @@ def bench_distributed(args, rank: int, world: int, local: int) -> Optional[dict]
     assert st == 0, f"rank {rank}: a flag wait timed out (status {st})"
 
     # ---- end to end: root-owned pinned host image -> N GPUs over N PCIe links -> pinned host image ----
+    rt.set_root_share(None)   # every rank has its own PCIe link: equal bands
     h_in = rt.shared_host("in", W * H * 3)
     h_out = rt.shared_host("out", W * H * 3)
     if rank == 0:
@@ -381,6 +437,9 @@ def bench_distributed(args, rank: int, world: int, local: int) -> Optional[dict]
                        "image": f"{W}x{H} RGB", "global_batch": 1, "seq_len": W * H, "parallelism": f"bands{world}",
                        "mode": "root-owned input and output on GPU 0; scatter and gather fused into the filter "
                                "kernel over NVLink peer memory (IPC), done flags acquired on the root each step",
+                       "bands": f"root GPU takes {share:.3f} of the rows (measured: its local rate vs the other ranks' "
+                                f"combined rate through the root's NVLink port), the other {world - 1} split the rest",
+                       "equal_bands_ms_per_step": round(ms_equal, 6),
                        "l2": "input 99.5 MB + output 99.5 MB per step; remote ranks bypass the root's L2 for peer traffic",
                        "timed_as": f"{K} steps per replay from C, CUDA events per rank, max over ranks, median of {args.repeats}"},
             "clocks": clk.summary(),
