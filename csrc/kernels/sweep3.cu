@@ -81,7 +81,7 @@ __device__ __forceinline__ void gray8(const uint8_t* s, const GrayRefCoef& gk, i
 }
 
 template <int GRAY, bool LUT0>
-__global__ void __launch_bounds__(kWarps * 32, 2)
+__global__ void __launch_bounds__(kWarps * 32, kSweepCtasPerSm)
 sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUtensorMap src_map,
               const __grid_constant__ CUtensorMap dst_map) {
   extern __shared__ __align__(1024) uint8_t smem[];

@@ -461,7 +461,7 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
   // segment height: a multiple of the box height, chosen so that the tasks fill the resident
   // warps evenly and the two halo rows per segment stay cheap
   P.n_strips = (L.W + kSweepStrip - 1) / kSweepStrip;
-  const int resident = sms * 2 * kSweepWarps;
+  const int resident = sms * kSweepCtasPerSm * kSweepWarps;
   double best = -1;
   for (int sr = 15; sr <= 96; sr += kSweepChunk) {
     const long long tasks = (long long)P.n_strips * ((y1 - y0 + sr - 1) / sr);
@@ -473,11 +473,11 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
     }
   }
   P.n_tasks = P.n_strips * ((y1 - y0 + P.seg_rows - 1) / P.seg_rows);
-  const int grid = std::max(1, std::min((P.n_tasks + kSweepWarps - 1) / kSweepWarps, sms * 2));
+  const int grid = std::max(1, std::min((P.n_tasks + kSweepWarps - 1) / kSweepWarps, sms * kSweepCtasPerSm));
   plan->info.last_tile_h = -P.seg_rows;  // negative: rows per sweep segment
   plan->info.last_smem_bytes = P.warp_smem * kSweepWarps;
   plan->info.last_grid = grid;
-  plan->info.last_blocks_per_sm = 2;
+  plan->info.last_blocks_per_sm = kSweepCtasPerSm;
   plan->info.last_tma_load = plan->info.last_tma_store = 1;
   plan->info.last_launches++;
   cudaError_t e = launch_sweep3(P, src_map, dst_map, grid, (cudaStream_t)L.stream);
