@@ -127,6 +127,7 @@ struct b2i_ctx {
   cudaEvent_t ev_src_ready = nullptr;
   uint32_t epoch = 0;
   bool peer_ok = true;
+  double root_share = 0;  // ROOT mode: fraction of the rows the root GPU keeps (0 = equal bands)
 };
 
 namespace {
@@ -247,6 +248,34 @@ extern "C" int b2i_ctx_load_root(b2i_ctx* c, const uint8_t* src, int W, int H, i
                              cudaMemcpyHostToDevice, r.stream));
   B2I_CUDA(cudaEventRecord(c->ev_src_ready, r.stream));
   for (int i = 0; i < c->n; ++i) b2i_band_rows(H, c->n, i, &c->devs[i].y0, &c->devs[i].y1);
+  if (c->root_share > 0 && c->n > 1) {
+    // link-aware plan: the root works out of its own HBM, everyone else through the root's one
+    // NVLink port, so the root keeps `root_share` of the rows and the others split the rest
+    const int cut = std::min(H, std::max(0, (int)(H * c->root_share + 0.5)));
+    int next = 0;
+    for (int k = 0; k < c->n; ++k) {
+      const int i = (c->root + k) % c->n;  // root first, then the others in rank order
+      Dev& d = c->devs[i];
+      if (k == 0) {
+        d.y0 = 0;
+        d.y1 = cut;
+        next = cut;
+      } else {
+        int a, b;
+        b2i_band_rows(H - cut, c->n - 1, k - 1, &a, &b);
+        d.y0 = cut + a;
+        d.y1 = cut + b;
+        next = d.y1;
+      }
+    }
+    (void)next;
+  }
+  return B2I_OK;
+}
+
+extern "C" int b2i_ctx_set_root_share(b2i_ctx* c, double share) {
+  B2I_CHECK_ARG(c && share >= 0 && share < 1, "share must be in [0,1)");
+  c->root_share = share;
   return B2I_OK;
 }
 

@@ -252,6 +252,10 @@ int b2i_ctx_gpus(const b2i_ctx_t* ctx);
 /* Host image -> the root GPU's source image (kernel.cu:110,163). */
 int b2i_ctx_load_root(b2i_ctx_t* ctx, const uint8_t* src, int W, int H, int C, size_t pitch,
                       int out_channels);
+/* ROOT mode band plan: the root GPU keeps `share` of the rows, the others split the rest (0 =
+ * equal bands). The root works out of its own HBM, every other GPU through the root's one NVLink
+ * port, so equal bands leave the root idle most of the step. Takes effect at the next load. */
+int b2i_ctx_set_root_share(b2i_ctx_t* ctx, double share);
 /* Root GPU's output image -> host (kernel.cu:202,223). Synchronises. */
 int b2i_ctx_fetch_root(b2i_ctx_t* ctx, uint8_t* dst, size_t pitch);
 /* ROOT mode: scatter and gather fused into the filter kernels (peer loads from / peer stores

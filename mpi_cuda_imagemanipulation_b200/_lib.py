@@ -162,6 +162,7 @@ _sig("b2i_ctx_create", C.c_int, C.c_int, _P(C.c_int), C.c_int, _P(C.c_void_p))
 _sig("b2i_ctx_destroy", None, C.c_void_p)
 _sig("b2i_ctx_gpus", C.c_int, C.c_void_p)
 _sig("b2i_ctx_load_root", C.c_int, C.c_void_p, u8p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_int)
+_sig("b2i_ctx_set_root_share", C.c_int, C.c_void_p, C.c_double)
 _sig("b2i_ctx_fetch_root", C.c_int, C.c_void_p, u8p, C.c_size_t)
 _sig("b2i_ctx_run_root", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, _P(C.c_double),
      _P(C.c_double))

@@ -58,10 +58,12 @@ class Runtime:
         return self._plans[key]
 
     def run(self, img: np.ndarray, chain, *, mode: str = "root", iters: int = 1, passes: int = 1,
-            sync: str = "events", no_tma: bool = False, **kw) -> np.ndarray:
+            sync: str = "events", no_tma: bool = False, root_share=None, **kw) -> np.ndarray:
         """Host image in, host image out.
 
         mode="root":     scatter/gather fused into the kernels through the root GPU's memory.
+                         root_share=f keeps f of the rows on the root GPU, "auto" measures the
+                         rates with equal bands first and balances (link-aware band plan).
         mode="resident": bands stay on their GPUs for ``passes`` applications of the chain,
                          halos pushed by the kernels; ``sync`` is "events" or "flags".
         mode="direct":   each GPU moves its band over its own PCIe link.
@@ -78,9 +80,23 @@ class Runtime:
             check(lib.b2i_ctx_run_direct(self._c, plan.handle, img.ctypes.data, W, H, Cn, W * Cn,
                                          out.ctypes.data, W * oc, flags, C.byref(ms)))
         else:
+            share = 0.0 if root_share in (None, "auto") else float(root_share)
+            check(lib.b2i_ctx_set_root_share(self._c, share if mode == "root" else 0.0))
             check(lib.b2i_ctx_load_root(self._c, img.ctypes.data, W, H, Cn, W * Cn, oc))
             if mode == "root":
                 check(lib.b2i_ctx_run_root(self._c, plan.handle, iters, flags, C.byref(ms), per))
+                if root_share == "auto" and self.gpus > 1:
+                    # measured rates with equal bands -> the share at which root and the rest finish together
+                    t = list(per)
+                    rows = [H * (i + 1) // self.gpus - H * i // self.gpus for i in range(self.gpus)]
+                    t_root = max(t[self.root], 1e-6)
+                    t_rem = max(max(x for i, x in enumerate(t) if i != self.root), 1e-6)
+                    r_root = rows[self.root] / t_root
+                    r_rem = sum(r for i, r in enumerate(rows) if i != self.root) / t_rem
+                    self.root_share = r_root / (r_root + r_rem)
+                    check(lib.b2i_ctx_set_root_share(self._c, self.root_share))
+                    check(lib.b2i_ctx_load_root(self._c, img.ctypes.data, W, H, Cn, W * Cn, oc))
+                    check(lib.b2i_ctx_run_root(self._c, plan.handle, iters, flags, C.byref(ms), per))
             elif mode == "resident":
                 check(lib.b2i_ctx_run_resident(self._c, plan.handle, passes, flags,
                                                int(sync == "flags"), C.byref(ms), per))

@@ -73,3 +73,12 @@ def test_topology_report():
     t = topology()
     assert len(t["devices"]) >= 1 and t["devices"][0]["sms"] > 0
     assert len(t["p2p"]) == len(t["devices"])
+
+
+@pytest.mark.parametrize("share", [0.5, 0.85, "auto"])
+def test_root_mode_link_aware_band_plan(share):
+    from mpi_cuda_imagemanipulation_b200.parallel import Runtime
+    img = b2.synth_image(1024, 403, seed=4)
+    with Runtime(gpus=4) as rt:
+        assert np.array_equal(rt.run(img, "kernel_cu", mode="root", root_share=share), b2.host_run("kernel_cu", img))
+        assert np.array_equal(rt.run(img, "gauss5,sobel", mode="root", root_share=share), b2.host_run("gauss5,sobel", img))
