@@ -510,15 +510,27 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
   int th = L.tile_h > 0 ? L.tile_h : env_int("B200IMG_TILE_H", 0);
   const int tiles_x = (L.W + kTileW - 1) / kTileW;
   if (th <= 0) {
-    const int cands[4] = {32, 24, 16, 8};
-    th = 8;
-    for (int c : cands) {
+    // Measured on 8K images (scripts/tile_h_sweep.py): the per-tile cost (barriers between
+    // phases, pipeline fill) is large, so tall tiles win. Two CTAs per SM with th >= 16 beat
+    // one CTA with th = 32, which beats anything with th = 8.
+    th = 0;
+    for (int c : {32, 24, 16}) {
       layout(seg, c, P);
       if (P.smem_bytes <= 113 * 1024) {
         th = c;
         break;
       }
     }
+    if (!th)
+      for (int c : {32, 24, 16}) {
+        layout(seg, c, P);
+        if (P.smem_bytes <= 227 * 1024) {
+          th = c;
+          break;
+        }
+      }
+    if (!th) th = 8;
+    // small images: shorter tiles so that every SM gets work
     while (th > 8 && tiles_x * ((y1 - y0 + th - 1) / th) < 2 * sms) th -= 8;
   }
   B2I_CHECK_ARG(th >= 4 && th <= kMaxTileH, "tile height %d out of range", th);
