@@ -694,15 +694,20 @@ tile_chain_kernel(const __grid_constant__ TileParams P, const __grid_constant__ 
   if (tid == 0 && (int)blockIdx.x < P.n_tiles) issue_load(blockIdx.x, 0);
   if (!P.use_tma_load) __syncthreads();  // the flag acquire of thread 0 orders everyone's loads
 
+  const bool prefetch = P.raw_stages == 2;
   for (int t = blockIdx.x; t < P.n_tiles; t += gridDim.x, ++it) {
-    const int s = it & 1;
+    const int s = prefetch ? (it & 1) : 0;
     const Tile T = tile_of(P, t);
     uint8_t* raw = smem + P.buf[BUF_RAW].off + s * P.raw_stage_bytes;
     const int tn = t + gridDim.x;
-    if (tid == 0 && tn < P.n_tiles) issue_load(tn, s ^ 1);  // stage s^1 was released by the
-                                                             // barrier ending the previous tile
+    if (prefetch) {
+      if (tid == 0 && tn < P.n_tiles) issue_load(tn, s ^ 1);  // stage s^1 was released by the
+                                                               // barrier ending the previous tile
+    } else if (tid == 0 && it > 0) {
+      issue_load(t, 0);  // single stage: the tile is loaded when its turn comes
+    }
     if (P.use_tma_load) {
-      mbar_wait(&full_bar[s], (it >> 1) & 1);
+      mbar_wait(&full_bar[s], prefetch ? ((it >> 1) & 1) : (it & 1));
     } else {
       load_tile_generic(P, T, raw);
       __syncthreads();

@@ -99,7 +99,8 @@ struct TileParams {
   uint64_t timeout_ns;
   // shared memory layout
   BufDesc buf[4];
-  int32_t raw_stage_bytes;   // BUF_RAW is double buffered: stage s lives at buf[0].off + s*raw_stage_bytes
+  int32_t raw_stages;        // 2: the next tile is prefetched while this one is filtered; 1: no prefetch, less smem
+  int32_t raw_stage_bytes;   // stage s of BUF_RAW lives at buf[0].off + s*raw_stage_bytes
   int32_t raw_rows, raw_tx_bytes;
   int32_t lut_off, bar_off, smem_bytes;
   PhaseDesc ph[kMaxPhases];

@@ -369,7 +369,7 @@ int align_up(int v, int a) { return (v + a - 1) / a * a; }
 
 // Shared-memory layout of a tile segment for tile height th. Every buffer starts 128-byte
 // aligned behind a 128-byte gap: stencil threads read 8 bytes to the left of a strip.
-void layout(const Segment& seg, int th, TileParams& P) {
+void layout(const Segment& seg, int th, TileParams& P, int raw_stages = 2) {
   const int R = seg.halo, rows_alloc = th + 2 * R + kRowGroup;
   int off = 0;
   auto place = [&](int bytes) {
@@ -384,7 +384,8 @@ void layout(const Segment& seg, int th, TileParams& P) {
   const int raw_pitch = kPlaneW * seg.cin;
   P.raw_tx_bytes = raw_pitch * P.raw_rows;
   P.raw_stage_bytes = align_up(raw_pitch * rows_alloc, 128) + 128;
-  P.buf[BUF_RAW] = {place(2 * P.raw_stage_bytes), raw_pitch, 0, 0};
+  P.raw_stages = raw_stages;
+  P.buf[BUF_RAW] = {place(raw_stages * P.raw_stage_bytes), raw_pitch, 0, 0};
   P.buf[BUF_A] = {seg.chan_a ? place(kPlaneW * seg.chan_a * rows_alloc) : 0, kPlaneW * seg.chan_a, 0, 0};
   P.buf[BUF_B] = {seg.chan_b ? place(kPlaneW * seg.chan_b * rows_alloc) : 0, kPlaneW * seg.chan_b, 0, 0};
   P.buf[BUF_STAGE] = {place(kTileW * seg.cout * th), kTileW * seg.cout, kApron, R};
@@ -508,6 +509,7 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
   // tile height: tallest that still lets two CTAs share an SM; smaller for small images so that
   // every SM gets tiles
   int th = L.tile_h > 0 ? L.tile_h : env_int("B200IMG_TILE_H", 0);
+  int raw_stages = env_int("B200IMG_RAW_STAGES", 2);
   const int tiles_x = (L.W + kTileW - 1) / kTileW;
   if (th <= 0) {
     // Measured on 8K images (scripts/tile_h_sweep.py): the per-tile cost (barriers between
@@ -515,11 +517,15 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
     // one CTA with th = 32, which beats anything with th = 8.
     th = 0;
     for (int c : {32, 24, 16}) {
-      layout(seg, c, P);
-      if (P.smem_bytes <= 113 * 1024) {
-        th = c;
-        break;
+      for (int st : {2, 1}) {  // without the prefetch stage a taller tile may still fit twice per SM
+        layout(seg, c, P, st);
+        if (P.smem_bytes <= 113 * 1024) {
+          th = c;
+          raw_stages = st;
+          break;
+        }
       }
+      if (th) break;
     }
     if (!th)
       for (int c : {32, 24, 16}) {
@@ -534,7 +540,7 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
     while (th > 8 && tiles_x * ((y1 - y0 + th - 1) / th) < 2 * sms) th -= 8;
   }
   B2I_CHECK_ARG(th >= 4 && th <= kMaxTileH, "tile height %d out of range", th);
-  layout(seg, th, P);
+  layout(seg, th, P, raw_stages == 1 ? 1 : 2);
   if (P.smem_bytes > 227 * 1024)
     B2I_FAIL(B2I_ERR_UNSUPPORTED, "segment needs %d bytes of shared memory", P.smem_bytes);
   P.W = L.W;
