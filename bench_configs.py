@@ -83,8 +83,11 @@ def main():
                 ms_equal = rt.last_ms
                 rt.run(img, chain, mode="root", iters=20, root_share="auto")   # link-aware bands
                 ms, share = rt.last_ms, getattr(rt, "root_share", None)
-            link_bytes = (n - 1) / n * W * H * (3 + (bpp - 3))  # in + out bytes crossing the root's link
-            roof_ms = max(W * H * bpp / n / (HBM * 1e6), link_bytes / 2 / (NVL * 1e6) if n > 1 else 0)
+            # roofline of the band plan actually used: the root's share at HBM speed, the rest through the
+            # root's NVLink port (input one way, output the other way, concurrently)
+            f_root = 1.0 if n == 1 else (share if share else 1.0 / n)
+            link_ms = (1 - f_root) * W * H * max(3, bpp - 3) / (NVL * 1e6)
+            roof_ms = max(f_root * W * H * bpp / (HBM * 1e6), link_ms)
             row[f"n{n}"] = {"ms": round(ms, 4), "mpix_per_s": round(mp / ms * 1e3, 1),
                             "equal_bands_ms": round(ms_equal, 4), "root_share": None if share is None else round(share, 3),
                             "roofline_ms": round(roof_ms, 4), "of_roofline": round(roof_ms / ms, 3)}
