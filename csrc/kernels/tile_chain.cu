@@ -123,36 +123,12 @@ __device__ void pw_phase(const TileParams& P, const PhaseDesc& ph, uint8_t* sbas
   const int R = P.halo, m = ph.margin, mc = ph.margin_x > 0 ? kMarginCols : 0;
   const int ux = (kTileW + 2 * mc) >> 2;  // units of 4 pixels per row
   const int rows = P.th + 2 * m;
-  const GrayRefCoef gk = gray_ref_coef(P.rgb_order);
   for (int idx = threadIdx.x; idx < ux * rows; idx += kTileThreads) {
     const int rr = idx / ux, u = idx - rr * ux;
     const int pr = R - m + rr, pc = kApron - mc + 4 * u;
     const uint8_t* s = sbase + (size_t)(pr - syorg) * spitch + (pc - sxorg) * ph.cin;
     uint8_t* d = dbase + (size_t)(pr - dyorg) * dpitch + (pc - dxorg) * ph.cout;
-    if (TYPE == PH_GRAY_REF || TYPE == PH_GRAY_CV) {
-      const uint32_t w0 = reinterpret_cast<const uint32_t*>(s)[0],
-                     w1 = reinterpret_cast<const uint32_t*>(s)[1],
-                     w2 = reinterpret_cast<const uint32_t*>(s)[2];
-      uint32_t g0, g1, g2, g3;
-      if (TYPE == PH_GRAY_REF) {
-        g0 = gray_ref_f23(byte_to_f23<0>(w0), byte_to_f23<1>(w0), byte_to_f23<2>(w0), gk);
-        g1 = gray_ref_f23(byte_to_f23<3>(w0), byte_to_f23<0>(w1), byte_to_f23<1>(w1), gk);
-        g2 = gray_ref_f23(byte_to_f23<2>(w1), byte_to_f23<3>(w1), byte_to_f23<0>(w2), gk);
-        g3 = gray_ref_f23(byte_to_f23<1>(w2), byte_to_f23<2>(w2), byte_to_f23<3>(w2), gk);
-      } else {
-        g0 = gray_cv_px(w0 & 0xFF, (w0 >> 8) & 0xFF, (w0 >> 16) & 0xFF, P.rgb_order);
-        g1 = gray_cv_px(w0 >> 24, w1 & 0xFF, (w1 >> 8) & 0xFF, P.rgb_order);
-        g2 = gray_cv_px((w1 >> 16) & 0xFF, w1 >> 24, w2 & 0xFF, P.rgb_order);
-        g3 = gray_cv_px((w2 >> 8) & 0xFF, (w2 >> 16) & 0xFF, w2 >> 24, P.rgb_order);
-      }
-      if (lut) {
-        g0 = lut[g0 & 0xFF];
-        g1 = lut[g1 & 0xFF];
-        g2 = lut[g2 & 0xFF];
-        g3 = lut[g3 & 0xFF];
-      }
-      *reinterpret_cast<uint32_t*>(d) = pack4_lo(g0, g1, g2, g3);
-    } else if (TYPE == PH_COPY) {
+    if (TYPE == PH_COPY) {
       for (int c = 0; c < ph.cin; ++c) {
         uint32_t w = reinterpret_cast<const uint32_t*>(s)[c];
         if (lut) w = lut4(lut, w);

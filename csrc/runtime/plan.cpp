@@ -394,12 +394,6 @@ void layout(const Segment& seg, int th, TileParams& P, int raw_stages = 2) {
   P.smem_bytes = align_up(off, 128);
 }
 
-struct DeviceInfo {
-  int sms = 0;
-  int bps_for_smem[2] = {0, 0};  // cache key: smem bytes -> blocks/SM
-  int bps = 0;
-};
-
 int device_sms(int dev, int* sms) {
   static int cache[64] = {0};
   if (dev >= 0 && dev < 64 && cache[dev]) {
