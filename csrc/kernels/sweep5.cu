@@ -1,0 +1,275 @@
+// The separable sweep kernel: a 5x5 (or 3x3) separable stencil on interleaved 3-channel data — the
+// 5x5 Gaussian of BASELINE.json configs 3-5 — as a warp-synchronous column sweep, the way sweep3.cu
+// runs the reference pipeline.
+//
+// The tile-chain kernel runs the same filter as two shared-memory phases at 0.24 of the HBM
+// roofline: half of its time is per-tile overhead (barriers, phase prologues) and the horizontal
+// pass is recomputed for the tile's vertical apron. Here:
+//   * a warp owns a strip of 240 pixels (30 lanes x 8 pixels x 3 bytes; lanes 0 and 31 only feed
+//     their neighbours) and walks down a segment of rows that arrive by TMA (5-row boxes);
+//   * the horizontal pass runs once per row in registers: taps at +-3 and +-6 bytes come from the
+//     lane's own 24 bytes and four warp shuffles, bytes are widened to 16-bit lanes (even / odd
+//     bytes of a word) and summed with packed integer multiply-adds;
+//   * the vertical pass keeps five rotating accumulator sets in registers; a horizontal row is
+//     added to the five output rows it touches and never stored. The row loop is unrolled by five
+//     so the roles of the sets are static;
+//   * image borders cost nothing per pixel: a mirrored or replicated row is the same data as a
+//     real row, so it only changes the five (warp-uniform) multipliers of that step;
+//   * finished rows are rounded, narrowed, staged per warp and leave by TMA store.
+// Exact: every lane stays below 65536 (normalised non-negative kernels, checked by the planner).
+#include "b200img.h"
+#include "device_utils.cuh"
+#include "sweep5.hpp"
+
+#include <type_traits>
+
+namespace b2i {
+using namespace dev;
+
+namespace {
+
+constexpr int CH = kS5Chunk;
+constexpr int NST = kS5Stages;
+
+__device__ __forceinline__ uint32_t lut4q(const uint8_t* lut, uint32_t w) {
+  const uint32_t a = lut[w & 0xFF], b = lut[(w >> 8) & 0xFF], c = lut[(w >> 16) & 0xFF], d = lut[w >> 24];
+  return pack4_lo(a, b, c, d);
+}
+
+// Bytes [O, O+4) of the 40-byte window {left4, left5, own0..own5, right0, right1}.
+template <int O>
+__device__ __forceinline__ uint32_t win40(const uint32_t (&a)[10]) {
+  static_assert(O >= 0 && O <= 36, "window outside the row registers");
+  if constexpr ((O & 3) == 0) return a[O >> 2];
+  else return __funnelshift_r(a[O >> 2], a[(O >> 2) + 1], (O & 3) * 8);
+}
+__device__ __forceinline__ uint32_t ev(uint32_t w) { return __byte_perm(w, 0u, 0x4240); }  // bytes 0,2 -> lanes
+__device__ __forceinline__ uint32_t od(uint32_t w) { return __byte_perm(w, 0u, 0x4341); }  // bytes 1,3 -> lanes
+
+// Horizontal taps for own word M (bytes 4M..4M+3 of the lane): even-lane and odd-lane sums.
+template <int M>
+__device__ __forceinline__ void hword(const uint32_t (&a)[10], const int (&w)[5], bool five, uint32_t& e,
+                                      uint32_t& o) {
+  constexpr int B = 8 + 4 * M;
+  const uint32_t s1 = win40<B - 3>(a), s2 = win40<B>(a), s3 = win40<B + 3>(a);
+  e = ev(s1) * w[1] + ev(s2) * w[2] + ev(s3) * w[3];
+  o = od(s1) * w[1] + od(s2) * w[2] + od(s3) * w[3];
+  if (five) {  // warp-uniform: a 3-tap kernel has w[0] == w[4] == 0
+    const uint32_t s0 = win40<B - 6>(a), s4 = win40<B + 6>(a);
+    e += ev(s0) * w[0] + ev(s4) * w[4];
+    o += od(s0) * w[0] + od(s4) * w[4];
+  }
+}
+
+// acc (+)= h * w over the 12 lane words of a row.
+template <bool INIT>
+__device__ __forceinline__ void vacc(uint32_t (&acc)[12], const uint32_t (&h)[12], uint32_t w) {
+#pragma unroll
+  for (int i = 0; i < 12; ++i) acc[i] = INIT ? h[i] * w : acc[i] + h[i] * w;
+}
+
+__global__ void __launch_bounds__(kS5Warps * 32, kS5CtasPerSm)
+sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CUtensorMap src_map,
+              const __grid_constant__ CUtensorMap dst_map) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ __align__(256) uint8_t lut1[256];
+  __shared__ __align__(8) uint64_t bars[kS5Warps * NST];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < 64; i += kS5Warps * 32)
+    reinterpret_cast<uint32_t*>(lut1)[i] = reinterpret_cast<const uint32_t*>(P.lut1)[i];
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kS5Warps * NST; ++i) mbar_init(&bars[i], 1);
+    fence_mbar_init();
+    tma_prefetch_desc(&src_map);
+    tma_prefetch_desc(&dst_map);
+  }
+  __syncthreads();  // the only block-wide barrier of the kernel
+
+  uint8_t* in_ring = smem + warp * P.warp_smem;          // NST stages of CH rows x kS5InBytes
+  uint8_t* out_ring = in_ring + NST * P.in_stage_bytes;  // 2 staging buffers of CH rows x kS5OutBytes
+  uint64_t* bar = &bars[warp * NST];
+  uint8_t* dummy = out_ring + 2 * P.out_buf_bytes + (lane == 0 ? 0 : 32);  // halo lanes store here
+  const bool halo_lane = lane == 0 || lane == 31;
+  int wh[5], wv[5];
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    wh[i] = P.wh[i];
+    wv[i] = P.wv[i];
+  }
+  const bool five = (P.wh[0] | P.wh[4]) != 0;
+  const uint32_t bias2 = (uint32_t)P.bias * 0x00010001u;
+  const int shift = P.shift;
+  const bool reflect = P.border == B2I_BORDER_REFLECT101, replicate = P.border == B2I_BORDER_REPLICATE;
+
+  uint32_t n_in = 0, n_out = 0;  // boxes consumed / stored by this warp so far
+  const int total_warps = gridDim.x * kS5Warps;
+  for (int task = blockIdx.x * kS5Warps + warp; task < P.n_tasks; task += total_warps) {
+    const int seg = task / P.n_strips, strip = task - seg * P.n_strips;
+    const int ya = P.y0 + seg * P.seg_rows, yb = min(P.y1, ya + P.seg_rows);  // output rows [ya, yb)
+    const int steps = yb - ya + 4;                   // input rows ya-2 .. yb+1
+    const int n_chunks = (steps + CH - 1) / CH;
+    const int xs = strip * kS5Strip;
+    const int x0 = xs - 8 + lane * 8;                // first pixel this lane holds
+    const int xw_in = (xs * 3 - 32) >> 2, xw_out = (xs * 3) >> 2;
+    if (lane == 0) {
+      for (int c = 0; c < min(NST, n_chunks); ++c) {
+        const uint32_t st = (n_in + c) % NST;
+        mbar_arrive_expect_tx(&bar[st], CH * kS5InBytes);
+        tma_load_2d(in_ring + st * P.in_stage_bytes, &src_map, xw_in, ya - 2 + c * CH - P.src_y_begin, &bar[st]);
+      }
+    }
+    const bool left_edge = x0 == 0, right_edge = x0 + 8 == P.W, beyond = x0 < 0 || x0 >= P.W;
+    const bool edge_fix = (reflect || replicate) && (xs == 0 || xs + kS5Strip >= P.W);  // warp-uniform
+    const bool vert_fix = (reflect || replicate) && (ya <= 2 || yb >= P.H - 2);        // warp-uniform
+
+    uint32_t X0[12], X1[12], X2[12], X3[12], X4[12];  // output row o collects in X[o mod 5]
+#pragma unroll
+    for (int i = 0; i < 12; ++i) X0[i] = X1[i] = X2[i] = X3[i] = X4[i] = 0;
+
+    // one input row: horizontal pass in registers, then into the five output rows it touches
+    auto step = [&](auto qc, int c, const uint8_t* stage_base, uint32_t ob_prev, uint32_t ob_cur,
+                    uint32_t (&K0)[12], uint32_t (&K1)[12], uint32_t (&K2)[12], uint32_t (&K3)[12],
+                    uint32_t (&K4)[12]) {
+      constexpr int q = decltype(qc)::value;
+      const int u = c * CH + q;
+      const int y = ya - 2 + u;
+      uint32_t a[10];
+      {
+        const uint8_t* s = stage_base + q * kS5InBytes + 8 + lane * 24;
+        const uint2 v0 = *reinterpret_cast<const uint2*>(s), v1 = *reinterpret_cast<const uint2*>(s + 8),
+                    v2 = *reinterpret_cast<const uint2*>(s + 16);
+        // rows outside the image (zero-filled by TMA) and lanes beyond the right edge contribute 0;
+        // mirrored / replicated rows are folded into the multipliers below
+        const bool valid = (unsigned)y < (unsigned)P.H && !beyond;
+        a[2] = valid ? v0.x : 0u; a[3] = valid ? v0.y : 0u; a[4] = valid ? v1.x : 0u;
+        a[5] = valid ? v1.y : 0u; a[6] = valid ? v2.x : 0u; a[7] = valid ? v2.y : 0u;
+      }
+      a[0] = __shfl_up_sync(0xFFFFFFFFu, a[6], 1);
+      a[1] = __shfl_up_sync(0xFFFFFFFFu, a[7], 1);
+      a[8] = __shfl_down_sync(0xFFFFFFFFu, a[2], 1);
+      a[9] = __shfl_down_sync(0xFFFFFFFFu, a[3], 1);
+      if (edge_fix) {
+        if (reflect) {  // pixels -1,-2 := pixels 1,2; pixels W,W+1 := pixels W-2,W-3
+          if (left_edge) {
+            a[1] = __byte_perm(__byte_perm(a[2], a[3], 0x5433), a[4], 0x3214);
+            a[0] = __byte_perm(a[3], 0u, 0x3200);
+          }
+          if (right_edge) {
+            a[8] = __byte_perm(__byte_perm(a[6], a[7], 0x4432), a[5], 0x7210);
+            a[9] = __byte_perm(a[6], 0u, 0x1010);
+          }
+        } else {        // replicate: pixels -1,-2 := pixel 0; pixels W,W+1 := pixel W-1
+          if (left_edge) {
+            a[1] = __byte_perm(a[2], 0u, 0x2102);
+            a[0] = __byte_perm(a[2], 0u, 0x1000);
+          }
+          if (right_edge) {
+            a[8] = __byte_perm(a[7], 0u, 0x1321);
+            a[9] = __byte_perm(a[7], 0u, 0x3232);
+          }
+        }
+      }
+      uint32_t h[12];
+      hword<0>(a, wh, five, h[0], h[1]);
+      hword<1>(a, wh, five, h[2], h[3]);
+      hword<2>(a, wh, five, h[4], h[5]);
+      hword<3>(a, wh, five, h[6], h[7]);
+      hword<4>(a, wh, five, h[8], h[9]);
+      hword<5>(a, wh, five, h[10], h[11]);
+      // multipliers of this row for the output rows y+2 (k0) .. y-2 (k4). A row that also stands
+      // for a mirrored / replicated row outside the image simply weighs more (warp-uniform).
+      int k0 = wv[0], k1 = wv[1], k2 = wv[2], k3 = wv[3], k4 = wv[4];
+      if (vert_fix) {
+        if (reflect) {
+          if (y == 1) { k2 += wv[0]; k3 += wv[1]; }
+          if (y == 2) { k4 += wv[0]; }
+          if (y == P.H - 2) { k1 += wv[3]; k2 += wv[4]; }
+          if (y == P.H - 3) { k0 += wv[4]; }
+        } else {
+          if (y == 0) { k1 += wv[0]; k2 += wv[1] + wv[0]; }
+          if (y == P.H - 1) { k2 += wv[3] + wv[4]; k3 += wv[4]; }
+        }
+      }
+      vacc<true>(K0, h, (uint32_t)k0);
+      vacc<false>(K1, h, (uint32_t)k1);
+      vacc<false>(K2, h, (uint32_t)k2);
+      vacc<false>(K3, h, (uint32_t)k3);
+      vacc<false>(K4, h, (uint32_t)k4);
+      // ---- output row y-2 (index e = u-4 of the task) is complete --------------------------------
+      if (u >= 4) {
+        constexpr int er = (q + 1) % 5;  // row of the store box
+        const uint32_t ob = er == 0 ? ob_cur : ob_prev;
+        if (er == 0) {                   // first row of a box: its previous store has read it
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          __syncwarp();
+        }
+        uint32_t r[6];
+#pragma unroll
+        for (int m = 0; m < 6; ++m) {
+          const uint32_t e = K4[2 * m] + bias2, o = K4[2 * m + 1] + bias2;
+          r[m] = shift == 8 ? __byte_perm(e, o, 0x7351)
+                            : (((e >> shift) & 0x00FF00FFu) | (((o >> shift) & 0x00FF00FFu) << 8));
+        }
+        if (P.has_lut1) {
+#pragma unroll
+          for (int m = 0; m < 6; ++m) r[m] = lut4q(lut1, r[m]);
+        }
+        uint2* d = reinterpret_cast<uint2*>(halo_lane ? dummy
+                                                      : out_ring + ob * P.out_buf_bytes + er * kS5OutBytes + (lane - 1) * 24);
+        d[0] = make_uint2(r[0], r[1]);
+        d[1] = make_uint2(r[2], r[3]);
+        d[2] = make_uint2(r[4], r[5]);
+        if (er == 4 || u == steps - 1) {  // a box of finished rows leaves by TMA
+          const int ec = (u - 4) / CH;
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&dst_map, xw_out, ya + ec * CH - P.y0, out_ring + ob * P.out_buf_bytes);
+            tma_store_commit();
+          }
+        }
+      }
+    };
+
+    for (int c = 0; c < n_chunks; ++c) {
+      const uint32_t st = (n_in + c) % NST;
+      const uint8_t* stage_base = in_ring + st * P.in_stage_bytes;
+      // output box c-1 is finished during rows 0..3 of input box c; box c starts at row 4
+      const uint32_t ob_prev = (n_out + c + 1) & 1, ob_cur = (n_out + c) & 1;
+      const int rows_here = min(CH, steps - c * CH);
+      mbar_wait(&bar[st], ((n_in + c) / NST) & 1);
+      step(std::integral_constant<int, 0>{}, c, stage_base, ob_prev, ob_cur, X2, X1, X0, X4, X3);
+      if (rows_here > 1) step(std::integral_constant<int, 1>{}, c, stage_base, ob_prev, ob_cur, X3, X2, X1, X0, X4);
+      if (rows_here > 2) step(std::integral_constant<int, 2>{}, c, stage_base, ob_prev, ob_cur, X4, X3, X2, X1, X0);
+      if (rows_here > 3) step(std::integral_constant<int, 3>{}, c, stage_base, ob_prev, ob_cur, X0, X4, X3, X2, X1);
+      if (rows_here > 4) step(std::integral_constant<int, 4>{}, c, stage_base, ob_prev, ob_cur, X1, X0, X4, X3, X2);
+      __syncwarp();  // every lane has read the box: the stage can take box c + NST
+      if (lane == 0 && c + NST < n_chunks) {
+        mbar_arrive_expect_tx(&bar[st], CH * kS5InBytes);
+        tma_load_2d(in_ring + st * P.in_stage_bytes, &src_map, xw_in, ya - 2 + (c + NST) * CH - P.src_y_begin,
+                    &bar[st]);
+      }
+    }
+    n_in += n_chunks;
+    n_out += (yb - ya + CH - 1) / CH;
+  }
+  if (lane == 0) tma_store_wait_all();
+}
+
+}  // namespace
+
+cudaError_t launch_sweep5(const Sweep5Params& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
+                          int grid, cudaStream_t stream) {
+  static bool configured[64] = {false};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 64 && !configured[dev]) {
+    e = cudaFuncSetAttribute(sweep5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return e;
+    configured[dev] = true;
+  }
+  sweep5_kernel<<<grid, kS5Warps * 32, P.warp_smem * kS5Warps, stream>>>(P, src_map, dst_map);
+  return cudaGetLastError();
+}
+}  // namespace b2i

@@ -1,0 +1,28 @@
+// Parameters of the separable sweep kernel (kernels/sweep5.cu), shared with the plan compiler.
+#pragma once
+#include <stdint.h>
+
+namespace b2i {
+
+constexpr int kS5Warps = 7;        // warps per CTA; 2 CTAs per SM = 14 warps (shared memory bound)
+constexpr int kS5CtasPerSm = 2;
+constexpr int kS5Strip = 240;      // output pixels per warp row: 30 lanes x 8 pixels (lanes 0, 31 are halo)
+constexpr int kS5InBytes = 800;    // TMA box width: 32 bytes left of the strip + 32 lanes x 24 bytes
+constexpr int kS5OutBytes = 720;   // 240 pixels x 3 channels
+constexpr int kS5Chunk = 5;        // rows per TMA box = period of the accumulator rotation
+constexpr int kS5Stages = 2;       // input boxes in flight per warp
+
+struct Sweep5Params {
+  int32_t W, H;
+  int32_t y0, y1;            // output rows of this launch
+  int32_t src_y_begin;       // global row of row 0 of the source tensor map
+  int32_t n_strips, seg_rows, n_tasks;
+  int32_t border;            // REFLECT101, REPLICATE or ZERO (REF goes to the tile kernel)
+  int32_t shift, bias;       // result = (sum + bias) >> shift
+  int32_t has_lut1;          // LUT applied to the result bytes
+  int32_t warp_smem, in_stage_bytes, out_buf_bytes;
+  int32_t wh[5], wv[5];      // horizontal / vertical taps (a 3-tap kernel has zeros at both ends)
+  uint8_t lut1[256];
+};
+
+}  // namespace b2i

@@ -18,6 +18,7 @@
 
 #include "../core/error.hpp"
 #include "../kernels/sweep3.hpp"
+#include "../kernels/sweep5.hpp"
 #include "../kernels/tile_plan.hpp"
 
 namespace b2i {
@@ -26,6 +27,8 @@ cudaError_t launch_tile_chain(const TileParams& P, const CUtensorMap& src_map,
                               const CUtensorMap& push_dn_map, int grid, cudaStream_t stream);
 cudaError_t tile_chain_occupancy(int smem_bytes, int* blocks_per_sm);
 cudaError_t launch_pointwise(const PointwiseParams& P, int grid, cudaStream_t stream);
+cudaError_t launch_sweep5(const Sweep5Params& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
+                          int grid, cudaStream_t stream);
 cudaError_t launch_sweep3(const SweepParams& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
                           int grid, cudaStream_t stream);
 int run_naive(const b2i_chain_t* chain, const uint8_t* src, int W, int H, int C, size_t src_pitch,
@@ -483,6 +486,73 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
   return 1;
 }
 
+// The separable sweep kernel (kernels/sweep5.cu) takes segments that are exactly one separable
+// stencil on 3-channel data (+LUT): the 5x5 / 3x3 Gaussians. Returns 1 if it launched, 0 if the
+// segment or the buffers do not qualify, -1 on a launch error.
+int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
+               const b2i_view_t& src, const b2i_view_t& dst, int sms) {
+  if (seg.phases.size() != 2 || env_int("B200IMG_NO_SWEEP", 0) || env_int("B200IMG_NO_SWEEP5", 0) ||
+      (L.flags & B2I_LAUNCH_NO_TMA) || env_int("B200IMG_NO_TMA", 0))
+    return 0;
+  const PhaseDesc& ph = seg.phases[0];
+  const PhaseDesc& pv = seg.phases[1];
+  if (ph.type != PH_SEPH || pv.type != PH_SEPV || seg.cin != 3 || seg.cout != 3 || pv.expand) return 0;
+  if (L.push_rows || L.wait_up_flag || L.wait_dn_flag || L.signal_up_flag || L.signal_dn_flag || L.done_flag)
+    return 0;
+  if ((L.W & 7) || L.W < 16 || L.H < 8 || y1 - y0 < 1) return 0;
+  Sweep5Params P;
+  memset(&P, 0, sizeof P);
+  P.W = L.W;
+  P.H = L.H;
+  P.y0 = y0;
+  P.y1 = y1;
+  P.src_y_begin = src.y_begin;
+  P.border = ph.border;
+  P.shift = pv.shift;
+  P.bias = pv.bias;
+  P.has_lut1 = pv.lut >= 0;
+  if (pv.lut >= 0) memcpy(P.lut1, seg.luts[pv.lut], 256);
+  const int off = ph.ksize == 5 ? 0 : 1;  // a 3-tap kernel sits in the middle of the five slots
+  for (int i = 0; i < ph.ksize; ++i) {
+    P.wh[i + off] = ph.sep[i];
+    P.wv[i + off] = pv.sep[i];
+  }
+  P.in_stage_bytes = align_up(kS5Chunk * kS5InBytes, 128);
+  P.out_buf_bytes = align_up(kS5Chunk * kS5OutBytes, 128);
+  P.warp_smem = kS5Stages * P.in_stage_bytes + 2 * P.out_buf_bytes + 128;
+  CUtensorMap src_map, dst_map;
+  const int src_rows = std::min(src.y_end, L.H) - src.y_begin;
+  if (!encode_map(&src_map, src.ptr, src.pitch, (int64_t)L.W * 3, src_rows, kS5InBytes, kS5Chunk)) return 0;
+  const uint64_t dptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
+  if (!encode_map(&dst_map, dptr, dst.pitch, (int64_t)L.W * 3, y1 - y0, kS5OutBytes, kS5Chunk)) return 0;
+  P.n_strips = (L.W + kS5Strip - 1) / kS5Strip;
+  const int resident = sms * kS5CtasPerSm * kS5Warps;
+  double best = -1;
+  for (int sr = 20; sr <= 120; sr += kS5Chunk) {  // multiples of the box height; 4 halo rows per segment
+    const long long tasks = (long long)P.n_strips * ((y1 - y0 + sr - 1) / sr);
+    const long long waves = (tasks + resident - 1) / resident;
+    const double eff = (double)tasks / (double)(waves * resident) * sr / (sr + 4.0);
+    if (eff > best + 1e-9) {
+      best = eff;
+      P.seg_rows = sr;
+    }
+  }
+  P.n_tasks = P.n_strips * ((y1 - y0 + P.seg_rows - 1) / P.seg_rows);
+  const int grid = std::max(1, std::min((P.n_tasks + kS5Warps - 1) / kS5Warps, sms * kS5CtasPerSm));
+  plan->info.last_tile_h = -P.seg_rows;
+  plan->info.last_smem_bytes = P.warp_smem * kS5Warps;
+  plan->info.last_grid = grid;
+  plan->info.last_blocks_per_sm = kS5CtasPerSm;
+  plan->info.last_tma_load = plan->info.last_tma_store = 1;
+  plan->info.last_launches++;
+  cudaError_t e = launch_sweep5(P, src_map, dst_map, grid, (cudaStream_t)L.stream);
+  if (e != cudaSuccess) {
+    b2i::fail(B2I_ERR_CUDA, __FILE__, __LINE__, "sweep5 launch: %s", cudaGetErrorString(e));
+    return -1;
+  }
+  return 1;
+}
+
 // One tile-kernel launch: rows [y0,y1) of this segment's result.
 int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
                         const b2i_view_t& src, const b2i_view_t& dst, bool first, bool last) {
@@ -494,7 +564,8 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
     const int need_a = std::max(0, y0 - seg.halo), need_b = std::min(L.H, y1 + seg.halo);
     B2I_CHECK_ARG(src.y_begin <= need_a && src.y_end >= need_b && dst.y_begin <= y0 && dst.y_end >= y1,
                   "views do not cover the band [%d,%d) and its halo", y0, y1);
-    const int sw = try_sweep(plan, seg, L, y0, y1, src, dst, sms);
+    int sw = try_sweep(plan, seg, L, y0, y1, src, dst, sms);
+    if (sw == 0) sw = try_sweep5(plan, seg, L, y0, y1, src, dst, sms);
     if (sw < 0) return B2I_ERR_CUDA;
     if (sw > 0) return B2I_OK;
   }
