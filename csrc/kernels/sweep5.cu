@@ -104,14 +104,30 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
   uint32_t n_in = 0, n_out = 0;  // boxes consumed / stored by this warp so far
   const int total_warps = gridDim.x * kS5Warps;
   for (int task = blockIdx.x * kS5Warps + warp; task < P.n_tasks; task += total_warps) {
-    const int seg = task / P.n_strips, strip = task - seg * P.n_strips;
+    // boundary segments first: their rows feed the neighbours' next pass
+    const int so = task / P.n_strips, strip = task - so * P.n_strips;
+    const int seg = so == 0 ? 0 : so == 1 ? P.n_segs - 1 : so - 1;
     const int ya = P.y0 + seg * P.seg_rows, yb = min(P.y1, ya + P.seg_rows);  // output rows [ya, yb)
     const int steps = yb - ya + 4;                   // input rows ya-2 .. yb+1
     const int n_chunks = (steps + CH - 1) / CH;
     const int xs = strip * kS5Strip;
     const int x0 = xs - 8 + lane * 8;                // first pixel this lane holds
     const int xw_in = (xs * 3 - 32) >> 2, xw_out = (xs * 3) >> 2;
+    // A task that reads ghost rows, or writes the neighbour's, first sees the neighbour's flag of
+    // the previous pass: its rows have landed here and it has finished reading what we overwrite.
+    const bool sig_up = P.signal_up_flag && ya < P.y0 + P.push_rows;
+    const bool sig_dn = P.signal_dn_flag && yb > P.y1 - P.push_rows;
     if (lane == 0) {
+      if (P.wait_up_flag && (ya - 2 < P.y0 || sig_up)) {
+        if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_up_flag), P.wait_epoch, P.timeout_ns))
+          atomicExch(reinterpret_cast<uint32_t*>(P.status), 1u);
+        asm volatile("fence.proxy.async;" ::: "memory");
+      }
+      if (P.wait_dn_flag && (yb + 2 > P.y1 || sig_dn)) {
+        if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_dn_flag), P.wait_epoch, P.timeout_ns))
+          atomicExch(reinterpret_cast<uint32_t*>(P.status), 2u);
+        asm volatile("fence.proxy.async;" ::: "memory");
+      }
       for (int c = 0; c < min(NST, n_chunks); ++c) {
         const uint32_t st = (n_in + c) % NST;
         mbar_arrive_expect_tx(&bar[st], CH * kS5InBytes);
@@ -219,6 +235,25 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
         d[0] = make_uint2(r[0], r[1]);
         d[1] = make_uint2(r[2], r[3]);
         d[2] = make_uint2(r[4], r[5]);
+        if (P.push_rows) {  // halo rows also go straight from registers into the neighbours' ghost rows
+          const int oy = y - 2;
+          if (!halo_lane && !beyond) {
+            const int64_t col = (int64_t)xs * 3 + (lane - 1) * 24;
+            if (P.push_up_ptr && oy < P.y0 + P.push_rows) {
+              uint2* g = reinterpret_cast<uint2*>(P.push_up_ptr + (int64_t)(oy - P.y0) * P.push_pitch + col);
+              g[0] = make_uint2(r[0], r[1]);
+              g[1] = make_uint2(r[2], r[3]);
+              g[2] = make_uint2(r[4], r[5]);
+            }
+            if (P.push_dn_ptr && oy >= P.y1 - P.push_rows) {
+              uint2* g = reinterpret_cast<uint2*>(P.push_dn_ptr +
+                                                  (int64_t)(oy - (P.y1 - P.push_rows)) * P.push_pitch + col);
+              g[0] = make_uint2(r[0], r[1]);
+              g[1] = make_uint2(r[2], r[3]);
+              g[2] = make_uint2(r[4], r[5]);
+            }
+          }
+        }
         if (er == 4 || u == steps - 1) {  // a box of finished rows leaves by TMA
           const int ec = (u - 4) / CH;
           fence_proxy_async_smem();
@@ -252,6 +287,21 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
     }
     n_in += n_chunks;
     n_out += (yb - ya + CH - 1) / CH;
+    if (sig_up || sig_dn) {  // count the task in; the last one releases the neighbour's flag
+      __threadfence_system();
+      __syncwarp();
+      if (lane == 0) {
+        uint32_t* counters = reinterpret_cast<uint32_t*>(P.counters);
+        if (sig_up && atomicAdd(&counters[0], 1u) + 1 == (uint32_t)P.n_up_tasks) {
+          atomicExch(&counters[0], 0u);
+          st_release_sys(reinterpret_cast<uint32_t*>(P.signal_up_flag), P.signal_epoch);
+        }
+        if (sig_dn && atomicAdd(&counters[1], 1u) + 1 == (uint32_t)P.n_dn_tasks) {
+          atomicExch(&counters[1], 0u);
+          st_release_sys(reinterpret_cast<uint32_t*>(P.signal_dn_flag), P.signal_epoch);
+        }
+      }
+    }
   }
   if (lane == 0) tma_store_wait_all();
 }

@@ -22,6 +22,14 @@ struct Sweep5Params {
   int32_t has_lut1;          // LUT applied to the result bytes
   int32_t warp_smem, in_stage_bytes, out_buf_bytes;
   int32_t wh[5], wv[5];      // horizontal / vertical taps (a 3-tap kernel has zeros at both ends)
+  // multi-GPU hooks (all zero on a single GPU): the first / last push_rows result rows are also
+  // stored into the neighbours' ghost rows, guarded by the same epoch flags as the tile kernel
+  int32_t push_rows, push_pitch;
+  int32_t n_segs, n_up_tasks, n_dn_tasks;  // tasks that count into the up / down signal
+  uint32_t wait_epoch, signal_epoch;
+  uint64_t push_up_ptr, push_dn_ptr;       // where row y0 / row y1 - push_rows lands at the neighbour
+  uint64_t wait_up_flag, wait_dn_flag, signal_up_flag, signal_dn_flag;
+  uint64_t counters, status, timeout_ns;
   uint8_t lut1[256];
 };
 

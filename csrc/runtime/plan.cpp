@@ -426,7 +426,8 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
   if ((g.type != PH_GRAY_REF && g.type != PH_GRAY_CV) || st.type != PH_STENCIL || st.ksize != 3 ||
       st.cin != 1 || seg.cin != 3)
     return 0;
-  if (L.push_rows || L.wait_up_flag || L.wait_dn_flag || L.signal_up_flag || L.signal_dn_flag || L.done_flag)
+  if ((L.push_rows && (L.push_up.ptr || L.push_dn.ptr)) || L.wait_up_flag || L.wait_dn_flag ||
+      L.signal_up_flag || L.signal_dn_flag || L.done_flag)
     return 0;
   if ((L.W & 7) || L.W < 16 || y1 - y0 < 1) return 0;
   SweepParams P;
@@ -490,16 +491,28 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
 // stencil on 3-channel data (+LUT): the 5x5 / 3x3 Gaussians. Returns 1 if it launched, 0 if the
 // segment or the buffers do not qualify, -1 on a launch error.
 int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
-               const b2i_view_t& src, const b2i_view_t& dst, int sms) {
+               const b2i_view_t& src, const b2i_view_t& dst, int sms, bool first, bool last) {
   if (seg.phases.size() != 2 || env_int("B200IMG_NO_SWEEP", 0) || env_int("B200IMG_NO_SWEEP5", 0) ||
       (L.flags & B2I_LAUNCH_NO_TMA) || env_int("B200IMG_NO_TMA", 0))
     return 0;
   const PhaseDesc& ph = seg.phases[0];
   const PhaseDesc& pv = seg.phases[1];
   if (ph.type != PH_SEPH || pv.type != PH_SEPV || seg.cin != 3 || seg.cout != 3 || pv.expand) return 0;
-  if (L.push_rows || L.wait_up_flag || L.wait_dn_flag || L.signal_up_flag || L.signal_dn_flag || L.done_flag)
-    return 0;
+  if (L.done_flag) return 0;
   if ((L.W & 7) || L.W < 16 || L.H < 8 || y1 - y0 < 1) return 0;
+  // multi-GPU hooks, with the tile kernel's meaning: waits guard the first segment's ghost-row
+  // reads, halo pushes and signals ride on the last segment's result rows
+  const bool pushes = last && L.push_rows > 0 && (L.push_up.ptr || L.push_dn.ptr);
+  const bool flags = (first && (L.wait_up_flag || L.wait_dn_flag)) || (last && (L.signal_up_flag || L.signal_dn_flag));
+  if (pushes) {
+    if (L.push_rows > y1 - y0 || L.push_rows > kGhostRows) return 0;  // the tile kernel reports the error
+    if (L.push_up.ptr && L.push_dn.ptr && L.push_up.pitch != L.push_dn.pitch) return 0;
+    const b2i_view_t& v = L.push_up.ptr ? L.push_up : L.push_dn;
+    if ((v.pitch & 7) || ((L.push_up.ptr | L.push_dn.ptr) & 7)) return 0;
+    if (L.push_up.ptr && (L.push_up.y_begin > y0 || L.push_up.y_end < y0 + L.push_rows)) return 0;
+    if (L.push_dn.ptr && (L.push_dn.y_begin > y1 - L.push_rows || L.push_dn.y_end < y1)) return 0;
+  }
+  if (flags && !(L.counters && L.status)) return 0;
   Sweep5Params P;
   memset(&P, 0, sizeof P);
   P.W = L.W;
@@ -537,7 +550,36 @@ int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0
       P.seg_rows = sr;
     }
   }
-  P.n_tasks = P.n_strips * ((y1 - y0 + P.seg_rows - 1) / P.seg_rows);
+  P.n_segs = (y1 - y0 + P.seg_rows - 1) / P.seg_rows;
+  P.n_tasks = P.n_strips * P.n_segs;
+  if (pushes || flags) {
+    P.push_rows = last ? L.push_rows : 0;
+    if (pushes) {
+      P.push_pitch = (int32_t)(L.push_up.ptr ? L.push_up.pitch : L.push_dn.pitch);
+      if (L.push_up.ptr)
+        P.push_up_ptr = L.push_up.ptr + (uint64_t)((int64_t)(y0 - L.push_up.y_begin) * L.push_up.pitch);
+      if (L.push_dn.ptr)
+        P.push_dn_ptr = L.push_dn.ptr +
+                        (uint64_t)((int64_t)(y1 - L.push_rows - L.push_dn.y_begin) * L.push_dn.pitch);
+    }
+    if (first) {
+      P.wait_up_flag = L.wait_up_flag;
+      P.wait_dn_flag = L.wait_dn_flag;
+      P.wait_epoch = L.wait_epoch;
+    }
+    if (last) {
+      P.signal_up_flag = L.signal_up_flag;
+      P.signal_dn_flag = L.signal_dn_flag;
+      P.signal_epoch = L.signal_epoch;
+    }
+    // segments whose rows reach into the first / last push_rows rows of the band (exact: the
+    // last of these tasks releases the neighbour's flag)
+    P.n_up_tasks = P.n_strips * ((P.push_rows + P.seg_rows - 1) / P.seg_rows);
+    P.n_dn_tasks = P.n_strips * (P.n_segs - (y1 - y0 - P.push_rows) / P.seg_rows);
+    P.counters = L.counters;
+    P.status = L.status;
+    P.timeout_ns = L.timeout_ns ? L.timeout_ns : 2000000000ull;
+  }
   const int grid = std::max(1, std::min((P.n_tasks + kS5Warps - 1) / kS5Warps, sms * kS5CtasPerSm));
   plan->info.last_tile_h = -P.seg_rows;
   plan->info.last_smem_bytes = P.warp_smem * kS5Warps;
@@ -565,7 +607,7 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
     B2I_CHECK_ARG(src.y_begin <= need_a && src.y_end >= need_b && dst.y_begin <= y0 && dst.y_end >= y1,
                   "views do not cover the band [%d,%d) and its halo", y0, y1);
     int sw = try_sweep(plan, seg, L, y0, y1, src, dst, sms);
-    if (sw == 0) sw = try_sweep5(plan, seg, L, y0, y1, src, dst, sms);
+    if (sw == 0) sw = try_sweep5(plan, seg, L, y0, y1, src, dst, sms, first, last);
     if (sw < 0) return B2I_ERR_CUDA;
     if (sw > 0) return B2I_OK;
   }
