@@ -1,0 +1,284 @@
+// The Sobel sweep kernel: out = clamp(|gx| + |gy|) per channel on interleaved 3-channel data (the
+// second half of BASELINE.json config 4, "blur -> Sobel"), as a warp-synchronous column sweep with
+// the skeleton of sweep5.cu: a warp owns a strip of 240 pixels and walks down a segment of rows
+// that arrive by TMA, results leave by TMA store, nothing but the warp's own rows is shared.
+//
+// Both Sobel kernels are separable, gx = [1 2 1]^T x [-1 0 1] and gy = [-1 0 1]^T x [1 2 1], so a
+// row is first reduced horizontally, in registers, to a difference D and a sum S per byte (taps at
+// +-3 bytes come from the lane's own 24 bytes and two warp shuffles). Bytes are widened to the two
+// 16-bit lanes of a word (even / odd bytes). D is signed: the lanes are kept as one 32-bit integer
+// hi * 65536 + lo with a signed lo, which 32-bit adds and multiplies keep exact; the bias 1024 added
+// with the last term makes both lanes non-negative again before they are looked at.
+//   gx(y-1) = D(y-2) + 2 D(y-1) + D(y)   -> one running partial sum and the previous D
+//   gy(y-1) = S(y) - S(y-2)              -> the two previous S rows, swapping roles every row
+// Mirrored / replicated rows beyond the top and bottom of the image are the same data as a real
+// row, so they only change three warp-uniform multipliers and which S rows are subtracted.
+#include "b200img.h"
+#include "device_utils.cuh"
+#include "sweep_sobel.hpp"
+
+#include <type_traits>
+
+namespace b2i {
+using namespace dev;
+
+namespace {
+
+constexpr int CH = kSSChunk;
+constexpr int NST = kSSStages;
+constexpr uint32_t kBias = 0x04000400u;  // 1024 per lane: |gx|, |gy| <= 1020
+
+__device__ __forceinline__ uint32_t lut4s(const uint8_t* lut, uint32_t w) {
+  const uint32_t a = lut[w & 0xFF], b = lut[(w >> 8) & 0xFF], c = lut[(w >> 16) & 0xFF], d = lut[w >> 24];
+  return pack4_lo(a, b, c, d);
+}
+
+// Bytes [O, O+4) of the 32-byte window {left5, own0..own5, right0}.
+template <int O>
+__device__ __forceinline__ uint32_t win32(const uint32_t (&a)[8]) {
+  static_assert(O >= 0 && O <= 28, "window outside the row registers");
+  if constexpr ((O & 3) == 0) return a[O >> 2];
+  else return __funnelshift_r(a[O >> 2], a[(O >> 2) + 1], (O & 3) * 8);
+}
+__device__ __forceinline__ uint32_t ev(uint32_t w) { return __byte_perm(w, 0u, 0x4240); }  // bytes 0,2 -> lanes
+__device__ __forceinline__ uint32_t od(uint32_t w) { return __byte_perm(w, 0u, 0x4341); }  // bytes 1,3 -> lanes
+
+// |v - 1024| + 1024 per lane, for lanes in [4, 2044]
+__device__ __forceinline__ uint32_t abs_biased(uint32_t v) { return __vmaxu2(v, 0x08000800u - v); }
+
+__global__ void __launch_bounds__(kSSWarps * 32, kSSCtasPerSm)
+sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_constant__ CUtensorMap src_map,
+                   const __grid_constant__ CUtensorMap dst_map) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ __align__(256) uint8_t lut1[256];
+  __shared__ __align__(8) uint64_t bars[kSSWarps * NST];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < 64; i += kSSWarps * 32)
+    reinterpret_cast<uint32_t*>(lut1)[i] = reinterpret_cast<const uint32_t*>(P.lut1)[i];
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kSSWarps * NST; ++i) mbar_init(&bars[i], 1);
+    fence_mbar_init();
+    tma_prefetch_desc(&src_map);
+    tma_prefetch_desc(&dst_map);
+  }
+  __syncthreads();  // the only block-wide barrier of the kernel
+
+  uint8_t* in_ring = smem + warp * P.warp_smem;          // NST stages of CH rows x kSSInBytes
+  uint8_t* out_ring = in_ring + NST * P.in_stage_bytes;  // 2 staging buffers of CH rows x kSSOutBytes
+  uint64_t* bar = &bars[warp * NST];
+  uint8_t* dummy = out_ring + 2 * P.out_buf_bytes + (lane == 0 ? 0 : 32);  // halo lanes store here
+  const bool halo_lane = lane == 0 || lane == 31;
+  const bool reflect = P.border == B2I_BORDER_REFLECT101, replicate = P.border == B2I_BORDER_REPLICATE;
+
+  uint32_t n_in = 0, n_out = 0;  // boxes consumed / stored by this warp so far
+  const int total_warps = gridDim.x * kSSWarps;
+  for (int task = blockIdx.x * kSSWarps + warp; task < P.n_tasks; task += total_warps) {
+    // boundary segments first: their rows feed the neighbours' next pass
+    const int so = task / P.n_strips, strip = task - so * P.n_strips;
+    const int seg = so == 0 ? 0 : so == 1 ? P.n_segs - 1 : so - 1;
+    const int ya = P.y0 + seg * P.seg_rows, yb = min(P.y1, ya + P.seg_rows);  // output rows [ya, yb)
+    const int steps = yb - ya + 2;                   // input rows ya-1 .. yb
+    const int n_chunks = (steps + CH - 1) / CH;
+    const int xs = strip * kSSStrip;
+    const int x0 = xs - 8 + lane * 8;                // first pixel this lane holds
+    const int xw_in = (xs * 3 - 32) >> 2, xw_out = (xs * 3) >> 2;
+    const bool sig_up = P.signal_up_flag && ya < P.y0 + P.push_rows;
+    const bool sig_dn = P.signal_dn_flag && yb > P.y1 - P.push_rows;
+    if (lane == 0) {
+      // a task that reads ghost rows, or writes the neighbour's, first sees the neighbour's flag
+      if (P.wait_up_flag && (ya - 1 < P.y0 || sig_up)) {
+        if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_up_flag), P.wait_epoch, P.timeout_ns))
+          atomicExch(reinterpret_cast<uint32_t*>(P.status), 1u);
+        asm volatile("fence.proxy.async;" ::: "memory");
+      }
+      if (P.wait_dn_flag && (yb + 1 > P.y1 || sig_dn)) {
+        if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_dn_flag), P.wait_epoch, P.timeout_ns))
+          atomicExch(reinterpret_cast<uint32_t*>(P.status), 2u);
+        asm volatile("fence.proxy.async;" ::: "memory");
+      }
+      for (int c = 0; c < min(NST, n_chunks); ++c) {
+        const uint32_t st = (n_in + c) % NST;
+        mbar_arrive_expect_tx(&bar[st], CH * kSSInBytes);
+        tma_load_2d(in_ring + st * P.in_stage_bytes, &src_map, xw_in, ya - 1 + c * CH - P.src_y_begin, &bar[st]);
+      }
+    }
+    const bool left_edge = x0 == 0, right_edge = x0 + 8 == P.W, beyond = x0 < 0 || x0 >= P.W;
+    const bool edge_fix = (reflect || replicate) && (xs == 0 || xs + kSSStrip >= P.W);  // warp-uniform
+    const bool vert_fix = (reflect || replicate) && (ya <= 1 || yb >= P.H - 1);        // warp-uniform
+
+    // per (word, even/odd) lane pair: running gx partial, previous D, the two previous S rows
+    uint32_t PA[12], DP[12], SA[12], SB[12];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) PA[i] = DP[i] = SA[i] = SB[i] = 0;
+
+    // one input row y; emits output row y-1. S1 holds S(y-1), S2 holds S(y-2) and takes S(y).
+    auto step = [&](auto qc, int c, const uint8_t* stage_base, uint32_t ob_prev, uint32_t ob_cur,
+                    uint32_t (&S1)[12], uint32_t (&S2)[12]) {
+      constexpr int q = decltype(qc)::value;
+      const int u = c * CH + q;
+      const int y = ya - 1 + u;
+      uint32_t a[8];
+      {
+        const uint8_t* s = stage_base + q * kSSInBytes + 8 + lane * 24;
+        const uint2 v0 = *reinterpret_cast<const uint2*>(s), v1 = *reinterpret_cast<const uint2*>(s + 8),
+                    v2 = *reinterpret_cast<const uint2*>(s + 16);
+        // rows outside the image (zero-filled by TMA) and lanes beyond the right edge contribute 0
+        const bool valid = (unsigned)y < (unsigned)P.H && !beyond;
+        a[1] = valid ? v0.x : 0u; a[2] = valid ? v0.y : 0u; a[3] = valid ? v1.x : 0u;
+        a[4] = valid ? v1.y : 0u; a[5] = valid ? v2.x : 0u; a[6] = valid ? v2.y : 0u;
+      }
+      a[0] = __shfl_up_sync(0xFFFFFFFFu, a[6], 1);
+      a[7] = __shfl_down_sync(0xFFFFFFFFu, a[1], 1);
+      if (edge_fix) {
+        if (reflect) {  // pixel -1 := pixel 1; pixel W := pixel W-2
+          if (left_edge) a[0] = __byte_perm(a[1], a[2], 0x5433);
+          if (right_edge) a[7] = __byte_perm(a[5], a[6], 0x4432);
+        } else {        // replicate: pixel -1 := pixel 0; pixel W := pixel W-1
+          if (left_edge) a[0] = __byte_perm(a[1], 0u, 0x2100);
+          if (right_edge) a[7] = __byte_perm(a[6], 0u, 0x3321);
+        }
+      }
+      // warp-uniform border rules of this row (see the header comment)
+      // gx(y-1) = PA + m3 D(y), PA' = m1 D(y-1) + m2 D(y); gy(y-1) = ka S(y) + kb S(y-1) + kc S(y-2)
+      uint32_t m1 = 1, m2 = 2, m3 = 1, ka = 1, kb = 0, kc = 0xFFFFFFFFu;
+      if (vert_fix) {
+        if (reflect) {
+          if (y == P.H - 1) m1 = 2;
+          if (y == 1) { m3 = 2; ka = 0; kc = 0; }  // S(-1) := S(1), the current row
+          if (y == P.H) kc = 0;                    // S(H) := S(H-2); S(H) itself is a zero row
+        } else {
+          if (y == 0 || y == P.H - 1) m2 = 3;
+          if (y == 1) { kb = 0xFFFFFFFFu; kc = 0; }  // S(-1) := S(0)
+          if (y == P.H) kb = 1;                      // S(H) := S(H-1)
+        }
+      }
+      constexpr int er = (q + 2) % CH;  // row of the store box
+      const uint32_t ob = er < 2 ? ob_cur : ob_prev;
+      if (u >= 2 && er == 0) {          // first row of a box: its previous store has read the buffer
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        __syncwarp();
+      }
+      uint32_t r[6];
+      auto word = [&](auto mc) {
+        constexpr int M = decltype(mc)::value;
+        constexpr int B = 4 + 4 * M;
+        const uint32_t sl = win32<B - 3>(a), sc = a[1 + M], sr = win32<B + 3>(a);
+        uint32_t res[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int i = 2 * M + h;
+          const uint32_t l = h ? od(sl) : ev(sl), cc = h ? od(sc) : ev(sc), rr = h ? od(sr) : ev(sr);
+          const uint32_t d = rr - l, s = l + rr + 2 * cc;
+          const uint32_t gx = PA[i] + d * m3;
+          const uint32_t gy = s * ka + kBias + S1[i] * kb + S2[i] * kc;
+          PA[i] = DP[i] * m1 + kBias + d * m2;
+          DP[i] = d;
+          S2[i] = s;
+          res[h] = __vminu2(abs_biased(gx) + abs_biased(gy), 0x08FF08FFu);  // low byte = clamp(|gx|+|gy|)
+        }
+        r[M] = __byte_perm(res[0], res[1], 0x6240);
+      };
+      word(std::integral_constant<int, 0>{});
+      word(std::integral_constant<int, 1>{});
+      word(std::integral_constant<int, 2>{});
+      word(std::integral_constant<int, 3>{});
+      word(std::integral_constant<int, 4>{});
+      word(std::integral_constant<int, 5>{});
+      // ---- output row y-1 (index e = u-2 of the task) ---------------------------------------------
+      if (u >= 2) {
+        if (P.has_lut1) {
+#pragma unroll
+          for (int m = 0; m < 6; ++m) r[m] = lut4s(lut1, r[m]);
+        }
+        uint2* d = reinterpret_cast<uint2*>(halo_lane ? dummy
+                                                      : out_ring + ob * P.out_buf_bytes + er * kSSOutBytes + (lane - 1) * 24);
+        d[0] = make_uint2(r[0], r[1]);
+        d[1] = make_uint2(r[2], r[3]);
+        d[2] = make_uint2(r[4], r[5]);
+        if (P.push_rows) {  // halo rows also go straight from registers into the neighbours' ghost rows
+          const int oy = y - 1;
+          if (!halo_lane && !beyond) {
+            const int64_t col = (int64_t)xs * 3 + (lane - 1) * 24;
+            if (P.push_up_ptr && oy < P.y0 + P.push_rows) {
+              uint2* g = reinterpret_cast<uint2*>(P.push_up_ptr + (int64_t)(oy - P.y0) * P.push_pitch + col);
+              g[0] = make_uint2(r[0], r[1]);
+              g[1] = make_uint2(r[2], r[3]);
+              g[2] = make_uint2(r[4], r[5]);
+            }
+            if (P.push_dn_ptr && oy >= P.y1 - P.push_rows) {
+              uint2* g = reinterpret_cast<uint2*>(P.push_dn_ptr +
+                                                  (int64_t)(oy - (P.y1 - P.push_rows)) * P.push_pitch + col);
+              g[0] = make_uint2(r[0], r[1]);
+              g[1] = make_uint2(r[2], r[3]);
+              g[2] = make_uint2(r[4], r[5]);
+            }
+          }
+        }
+        if (er == CH - 1 || u == steps - 1) {  // a box of finished rows leaves by TMA
+          const int ec = (u - 2) / CH;
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&dst_map, xw_out, ya + ec * CH - P.y0, out_ring + ob * P.out_buf_bytes);
+            tma_store_commit();
+          }
+        }
+      }
+    };
+
+    for (int c = 0; c < n_chunks; ++c) {
+      const uint32_t st = (n_in + c) % NST;
+      const uint8_t* stage_base = in_ring + st * P.in_stage_bytes;
+      // output box c-1 is finished during rows 0..1 of input box c; box c starts at row 2
+      const uint32_t ob_prev = (n_out + c + 1) & 1, ob_cur = (n_out + c) & 1;
+      const int rows_here = min(CH, steps - c * CH);
+      mbar_wait(&bar[st], ((n_in + c) / NST) & 1);
+      step(std::integral_constant<int, 0>{}, c, stage_base, ob_prev, ob_cur, SA, SB);
+      if (rows_here > 1) step(std::integral_constant<int, 1>{}, c, stage_base, ob_prev, ob_cur, SB, SA);
+      if (rows_here > 2) step(std::integral_constant<int, 2>{}, c, stage_base, ob_prev, ob_cur, SA, SB);
+      if (rows_here > 3) step(std::integral_constant<int, 3>{}, c, stage_base, ob_prev, ob_cur, SB, SA);
+      __syncwarp();  // every lane has read the box: the stage can take box c + NST
+      if (lane == 0 && c + NST < n_chunks) {
+        mbar_arrive_expect_tx(&bar[st], CH * kSSInBytes);
+        tma_load_2d(in_ring + st * P.in_stage_bytes, &src_map, xw_in, ya - 1 + (c + NST) * CH - P.src_y_begin,
+                    &bar[st]);
+      }
+    }
+    n_in += n_chunks;
+    n_out += (yb - ya + CH - 1) / CH;
+    if (sig_up || sig_dn) {  // count the task in; the last one releases the neighbour's flag
+      __threadfence_system();
+      __syncwarp();
+      if (lane == 0) {
+        uint32_t* counters = reinterpret_cast<uint32_t*>(P.counters);
+        if (sig_up && atomicAdd(&counters[0], 1u) + 1 == (uint32_t)P.n_up_tasks) {
+          atomicExch(&counters[0], 0u);
+          st_release_sys(reinterpret_cast<uint32_t*>(P.signal_up_flag), P.signal_epoch);
+        }
+        if (sig_dn && atomicAdd(&counters[1], 1u) + 1 == (uint32_t)P.n_dn_tasks) {
+          atomicExch(&counters[1], 0u);
+          st_release_sys(reinterpret_cast<uint32_t*>(P.signal_dn_flag), P.signal_epoch);
+        }
+      }
+    }
+  }
+  if (lane == 0) tma_store_wait_all();
+}
+
+}  // namespace
+
+cudaError_t launch_sweep_sobel(const SweepSobelParams& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
+                               int grid, cudaStream_t stream) {
+  static bool configured[64] = {false};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 64 && !configured[dev]) {
+    e = cudaFuncSetAttribute(sweep_sobel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return e;
+    configured[dev] = true;
+  }
+  sweep_sobel_kernel<<<grid, kSSWarps * 32, P.warp_smem * kSSWarps, stream>>>(P, src_map, dst_map);
+  return cudaGetLastError();
+}
+}  // namespace b2i

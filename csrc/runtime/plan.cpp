@@ -19,6 +19,7 @@
 #include "../core/error.hpp"
 #include "../kernels/sweep3.hpp"
 #include "../kernels/sweep5.hpp"
+#include "../kernels/sweep_sobel.hpp"
 #include "../kernels/tile_plan.hpp"
 
 namespace b2i {
@@ -29,6 +30,8 @@ cudaError_t tile_chain_occupancy(int smem_bytes, int* blocks_per_sm);
 cudaError_t launch_pointwise(const PointwiseParams& P, int grid, cudaStream_t stream);
 cudaError_t launch_sweep5(const Sweep5Params& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
                           int grid, cudaStream_t stream);
+cudaError_t launch_sweep_sobel(const SweepSobelParams& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
+                               int grid, cudaStream_t stream);
 cudaError_t launch_sweep3(const SweepParams& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
                           int grid, cudaStream_t stream);
 int run_naive(const b2i_chain_t* chain, const uint8_t* src, int W, int H, int C, size_t src_pitch,
@@ -156,6 +159,10 @@ struct b2i_plan {
   b2i_chain_t chain;
   int cin = 0, cout = 0, halo = 0;
   std::vector<Segment> segs;
+  // The same chain cut so that every stencil the sweep kernels take stands alone (empty if that is
+  // the same cut). Two sweep launches beat one fused tile launch (8K gauss5,sobel: 290 us fused,
+  // 89 + 62 us split), but only where the sweeps can run: b2i_cuda_run picks per launch.
+  std::vector<Segment> segs_split;
   b2i_plan_info_t info;
 };
 
@@ -339,6 +346,9 @@ bool build_pointwise_segment(const std::vector<Elem>& el, int cin, Segment& seg)
   return true;
 }
 
+int align_up(int v, int a);
+void layout(const Segment& seg, int th, TileParams& P, int raw_stages);
+
 PFN_cuTensorMapEncodeTiled_v12000 tensor_map_encoder() {
   static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
   static std::once_flag once;
@@ -395,6 +405,54 @@ void layout(const Segment& seg, int th, TileParams& P, int raw_stages = 2) {
   P.lut_off = place(kMaxLuts * 256);
   P.bar_off = place(64);
   P.smem_bytes = align_up(off, 128);
+}
+
+// A segment the sweep kernels sweep5.cu / sweep_sobel.cu take (given a fitting image).
+bool sweep_shape(const Segment& seg) {
+  if (seg.pointwise || seg.cin != 3 || seg.cout != 3) return false;
+  if (seg.phases.size() == 2)
+    return seg.phases[0].type == PH_SEPH && seg.phases[1].type == PH_SEPV && !seg.phases[1].expand;
+  return seg.phases.size() == 1 && seg.phases[0].type == PH_SOBEL && !seg.phases[0].expand &&
+         seg.phases[0].border != B2I_BORDER_REF;
+}
+
+// Greedy segmentation: extend the segment while the tile kernel can still absorb it. With
+// `split`, a segment the sweep kernels take is closed instead of being fused with what follows.
+int segment_chain(const std::vector<Elem>& el, int in_channels, bool split, std::vector<Segment>& out) {
+  out.clear();
+  size_t i = 0;
+  int c = in_channels;
+  while (i < el.size()) {
+    Segment best;
+    size_t best_end = i;
+    bool have = false;
+    for (size_t end = i + 1; end <= el.size(); ++end) {
+      std::vector<Elem> sub(el.begin() + i, el.begin() + end);
+      bool stencil = false;
+      for (const Elem& e : sub) stencil = stencil || e.kind == B2I_OP_STENCIL || e.kind == B2I_OP_SOBEL;
+      Segment seg;
+      bool ok = false;
+      if (!stencil) ok = build_pointwise_segment(sub, c, seg);
+      if (!ok) ok = build_tile_segment(sub, c, seg) == B2I_OK;
+      if (ok) {
+        TileParams P;  // also has to fit in shared memory at the smallest tile height
+        if (!seg.pointwise) {
+          layout(seg, 8, P);
+          ok = P.smem_bytes <= 227 * 1024;
+        }
+      }
+      if (!ok) break;
+      if (split && have && sweep_shape(best) && !sweep_shape(seg)) break;
+      best = seg;
+      best_end = end;
+      have = true;
+    }
+    if (!have) return B2I_ERR_UNSUPPORTED;
+    c = best.cout;
+    out.push_back(best);
+    i = best_end;
+  }
+  return B2I_OK;
 }
 
 int device_sms(int dev, int* sms) {
@@ -487,6 +545,72 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
   return 1;
 }
 
+// Multi-GPU hooks of the sweep kernels (sweep5.cu, sweep_sobel.cu), with the tile kernel's meaning:
+// waits guard the first segment's ghost-row reads, halo pushes and signals ride on the last
+// segment's result rows. Returns false if the launch asks for something the sweeps do not do (the
+// tile kernel then runs it, or reports the error).
+bool sweep_hooks_ok(const b2i_launch_t& L, int y0, int y1, bool first, bool last, bool* pushes, bool* flags) {
+  if (L.done_flag) return false;
+  *pushes = last && L.push_rows > 0 && (L.push_up.ptr || L.push_dn.ptr);
+  *flags = (first && (L.wait_up_flag || L.wait_dn_flag)) || (last && (L.signal_up_flag || L.signal_dn_flag));
+  if (*pushes) {
+    if (L.push_rows > y1 - y0 || L.push_rows > kGhostRows) return false;
+    if (L.push_up.ptr && L.push_dn.ptr && L.push_up.pitch != L.push_dn.pitch) return false;
+    const b2i_view_t& v = L.push_up.ptr ? L.push_up : L.push_dn;
+    if ((v.pitch & 7) || ((L.push_up.ptr | L.push_dn.ptr) & 7)) return false;
+    if (L.push_up.ptr && (L.push_up.y_begin > y0 || L.push_up.y_end < y0 + L.push_rows)) return false;
+    if (L.push_dn.ptr && (L.push_dn.y_begin > y1 - L.push_rows || L.push_dn.y_end < y1)) return false;
+  }
+  if (*flags && !(L.counters && L.status)) return false;
+  return true;
+}
+
+template <class Params>
+void sweep_hooks_fill(Params& P, const b2i_launch_t& L, int y0, int y1, bool first, bool last, bool pushes) {
+  P.push_rows = last ? L.push_rows : 0;
+  if (pushes) {
+    P.push_pitch = (int32_t)(L.push_up.ptr ? L.push_up.pitch : L.push_dn.pitch);
+    if (L.push_up.ptr)
+      P.push_up_ptr = L.push_up.ptr + (uint64_t)((int64_t)(y0 - L.push_up.y_begin) * L.push_up.pitch);
+    if (L.push_dn.ptr)
+      P.push_dn_ptr = L.push_dn.ptr + (uint64_t)((int64_t)(y1 - L.push_rows - L.push_dn.y_begin) * L.push_dn.pitch);
+  }
+  if (first) {
+    P.wait_up_flag = L.wait_up_flag;
+    P.wait_dn_flag = L.wait_dn_flag;
+    P.wait_epoch = L.wait_epoch;
+  }
+  if (last) {
+    P.signal_up_flag = L.signal_up_flag;
+    P.signal_dn_flag = L.signal_dn_flag;
+    P.signal_epoch = L.signal_epoch;
+  }
+  // segments whose rows reach into the first / last push_rows rows of the band (exact: the last
+  // of these tasks releases the neighbour's flag)
+  P.n_up_tasks = P.n_strips * ((P.push_rows + P.seg_rows - 1) / P.seg_rows);
+  P.n_dn_tasks = P.n_strips * (P.n_segs - (y1 - y0 - P.push_rows) / P.seg_rows);
+  P.counters = L.counters;
+  P.status = L.status;
+  P.timeout_ns = L.timeout_ns ? L.timeout_ns : 2000000000ull;
+}
+
+// Rows per sweep segment: a multiple of the box height, chosen so that the tasks fill the resident
+// warps evenly and the halo rows read twice per segment stay cheap.
+int sweep_seg_rows(int n_strips, int rows, int resident, int chunk, int lo, int hi, int halo_rows) {
+  double best = -1;
+  int pick = lo;
+  for (int sr = lo; sr <= hi; sr += chunk) {
+    const long long tasks = (long long)n_strips * ((rows + sr - 1) / sr);
+    const long long waves = (tasks + resident - 1) / resident;
+    const double eff = (double)tasks / (double)(waves * resident) * sr / (sr + (double)halo_rows);
+    if (eff > best + 1e-9) {
+      best = eff;
+      pick = sr;
+    }
+  }
+  return pick;
+}
+
 // The separable sweep kernel (kernels/sweep5.cu) takes segments that are exactly one separable
 // stencil on 3-channel data (+LUT): the 5x5 / 3x3 Gaussians. Returns 1 if it launched, 0 if the
 // segment or the buffers do not qualify, -1 on a launch error.
@@ -498,21 +622,9 @@ int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0
   const PhaseDesc& ph = seg.phases[0];
   const PhaseDesc& pv = seg.phases[1];
   if (ph.type != PH_SEPH || pv.type != PH_SEPV || seg.cin != 3 || seg.cout != 3 || pv.expand) return 0;
-  if (L.done_flag) return 0;
   if ((L.W & 7) || L.W < 16 || L.H < 8 || y1 - y0 < 1) return 0;
-  // multi-GPU hooks, with the tile kernel's meaning: waits guard the first segment's ghost-row
-  // reads, halo pushes and signals ride on the last segment's result rows
-  const bool pushes = last && L.push_rows > 0 && (L.push_up.ptr || L.push_dn.ptr);
-  const bool flags = (first && (L.wait_up_flag || L.wait_dn_flag)) || (last && (L.signal_up_flag || L.signal_dn_flag));
-  if (pushes) {
-    if (L.push_rows > y1 - y0 || L.push_rows > kGhostRows) return 0;  // the tile kernel reports the error
-    if (L.push_up.ptr && L.push_dn.ptr && L.push_up.pitch != L.push_dn.pitch) return 0;
-    const b2i_view_t& v = L.push_up.ptr ? L.push_up : L.push_dn;
-    if ((v.pitch & 7) || ((L.push_up.ptr | L.push_dn.ptr) & 7)) return 0;
-    if (L.push_up.ptr && (L.push_up.y_begin > y0 || L.push_up.y_end < y0 + L.push_rows)) return 0;
-    if (L.push_dn.ptr && (L.push_dn.y_begin > y1 - L.push_rows || L.push_dn.y_end < y1)) return 0;
-  }
-  if (flags && !(L.counters && L.status)) return 0;
+  bool pushes = false, flags = false;
+  if (!sweep_hooks_ok(L, y0, y1, first, last, &pushes, &flags)) return 0;
   Sweep5Params P;
   memset(&P, 0, sizeof P);
   P.W = L.W;
@@ -540,46 +652,10 @@ int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0
   if (!encode_map(&dst_map, dptr, dst.pitch, (int64_t)L.W * 3, y1 - y0, kS5OutBytes, kS5Chunk)) return 0;
   P.n_strips = (L.W + kS5Strip - 1) / kS5Strip;
   const int resident = sms * kS5CtasPerSm * kS5Warps;
-  double best = -1;
-  for (int sr = 20; sr <= 120; sr += kS5Chunk) {  // multiples of the box height; 4 halo rows per segment
-    const long long tasks = (long long)P.n_strips * ((y1 - y0 + sr - 1) / sr);
-    const long long waves = (tasks + resident - 1) / resident;
-    const double eff = (double)tasks / (double)(waves * resident) * sr / (sr + 4.0);
-    if (eff > best + 1e-9) {
-      best = eff;
-      P.seg_rows = sr;
-    }
-  }
+  P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kS5Chunk, 20, 120, 4);
   P.n_segs = (y1 - y0 + P.seg_rows - 1) / P.seg_rows;
   P.n_tasks = P.n_strips * P.n_segs;
-  if (pushes || flags) {
-    P.push_rows = last ? L.push_rows : 0;
-    if (pushes) {
-      P.push_pitch = (int32_t)(L.push_up.ptr ? L.push_up.pitch : L.push_dn.pitch);
-      if (L.push_up.ptr)
-        P.push_up_ptr = L.push_up.ptr + (uint64_t)((int64_t)(y0 - L.push_up.y_begin) * L.push_up.pitch);
-      if (L.push_dn.ptr)
-        P.push_dn_ptr = L.push_dn.ptr +
-                        (uint64_t)((int64_t)(y1 - L.push_rows - L.push_dn.y_begin) * L.push_dn.pitch);
-    }
-    if (first) {
-      P.wait_up_flag = L.wait_up_flag;
-      P.wait_dn_flag = L.wait_dn_flag;
-      P.wait_epoch = L.wait_epoch;
-    }
-    if (last) {
-      P.signal_up_flag = L.signal_up_flag;
-      P.signal_dn_flag = L.signal_dn_flag;
-      P.signal_epoch = L.signal_epoch;
-    }
-    // segments whose rows reach into the first / last push_rows rows of the band (exact: the
-    // last of these tasks releases the neighbour's flag)
-    P.n_up_tasks = P.n_strips * ((P.push_rows + P.seg_rows - 1) / P.seg_rows);
-    P.n_dn_tasks = P.n_strips * (P.n_segs - (y1 - y0 - P.push_rows) / P.seg_rows);
-    P.counters = L.counters;
-    P.status = L.status;
-    P.timeout_ns = L.timeout_ns ? L.timeout_ns : 2000000000ull;
-  }
+  if (pushes || flags) sweep_hooks_fill(P, L, y0, y1, first, last, pushes);
   const int grid = std::max(1, std::min((P.n_tasks + kS5Warps - 1) / kS5Warps, sms * kS5CtasPerSm));
   plan->info.last_tile_h = -P.seg_rows;
   plan->info.last_smem_bytes = P.warp_smem * kS5Warps;
@@ -590,6 +666,57 @@ int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0
   cudaError_t e = launch_sweep5(P, src_map, dst_map, grid, (cudaStream_t)L.stream);
   if (e != cudaSuccess) {
     b2i::fail(B2I_ERR_CUDA, __FILE__, __LINE__, "sweep5 launch: %s", cudaGetErrorString(e));
+    return -1;
+  }
+  return 1;
+}
+
+// The Sobel sweep kernel (kernels/sweep_sobel.cu) takes segments that are exactly one Sobel
+// magnitude on 3-channel data (+LUT). Same return values as try_sweep5.
+int try_sweep_sobel(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
+                    const b2i_view_t& src, const b2i_view_t& dst, int sms, bool first, bool last) {
+  if (seg.phases.size() != 1 || env_int("B200IMG_NO_SWEEP", 0) || env_int("B200IMG_NO_SWEEP_SOBEL", 0) ||
+      (L.flags & B2I_LAUNCH_NO_TMA) || env_int("B200IMG_NO_TMA", 0))
+    return 0;
+  const PhaseDesc& ph = seg.phases[0];
+  if (ph.type != PH_SOBEL || seg.cin != 3 || seg.cout != 3 || ph.expand || ph.border == B2I_BORDER_REF) return 0;
+  if ((L.W & 7) || L.W < 16 || L.H < 8 || y1 - y0 < 1) return 0;
+  bool pushes = false, flags = false;
+  if (!sweep_hooks_ok(L, y0, y1, first, last, &pushes, &flags)) return 0;
+  SweepSobelParams P;
+  memset(&P, 0, sizeof P);
+  P.W = L.W;
+  P.H = L.H;
+  P.y0 = y0;
+  P.y1 = y1;
+  P.src_y_begin = src.y_begin;
+  P.border = ph.border;
+  P.has_lut1 = ph.lut >= 0;
+  if (ph.lut >= 0) memcpy(P.lut1, seg.luts[ph.lut], 256);
+  P.in_stage_bytes = align_up(kSSChunk * kSSInBytes, 128);
+  P.out_buf_bytes = align_up(kSSChunk * kSSOutBytes, 128);
+  P.warp_smem = kSSStages * P.in_stage_bytes + 2 * P.out_buf_bytes + 128;
+  CUtensorMap src_map, dst_map;
+  const int src_rows = std::min(src.y_end, L.H) - src.y_begin;
+  if (!encode_map(&src_map, src.ptr, src.pitch, (int64_t)L.W * 3, src_rows, kSSInBytes, kSSChunk)) return 0;
+  const uint64_t dptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
+  if (!encode_map(&dst_map, dptr, dst.pitch, (int64_t)L.W * 3, y1 - y0, kSSOutBytes, kSSChunk)) return 0;
+  P.n_strips = (L.W + kSSStrip - 1) / kSSStrip;
+  const int resident = sms * kSSCtasPerSm * kSSWarps;
+  P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kSSChunk, 16, 120, 2);
+  P.n_segs = (y1 - y0 + P.seg_rows - 1) / P.seg_rows;
+  P.n_tasks = P.n_strips * P.n_segs;
+  if (pushes || flags) sweep_hooks_fill(P, L, y0, y1, first, last, pushes);
+  const int grid = std::max(1, std::min((P.n_tasks + kSSWarps - 1) / kSSWarps, sms * kSSCtasPerSm));
+  plan->info.last_tile_h = -P.seg_rows;
+  plan->info.last_smem_bytes = P.warp_smem * kSSWarps;
+  plan->info.last_grid = grid;
+  plan->info.last_blocks_per_sm = kSSCtasPerSm;
+  plan->info.last_tma_load = plan->info.last_tma_store = 1;
+  plan->info.last_launches++;
+  cudaError_t e = launch_sweep_sobel(P, src_map, dst_map, grid, (cudaStream_t)L.stream);
+  if (e != cudaSuccess) {
+    b2i::fail(B2I_ERR_CUDA, __FILE__, __LINE__, "sweep_sobel launch: %s", cudaGetErrorString(e));
     return -1;
   }
   return 1;
@@ -608,6 +735,7 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
                   "views do not cover the band [%d,%d) and its halo", y0, y1);
     int sw = try_sweep(plan, seg, L, y0, y1, src, dst, sms);
     if (sw == 0) sw = try_sweep5(plan, seg, L, y0, y1, src, dst, sms, first, last);
+    if (sw == 0) sw = try_sweep_sobel(plan, seg, L, y0, y1, src, dst, sms, first, last);
     if (sw < 0) return B2I_ERR_CUDA;
     if (sw > 0) return B2I_OK;
   }
@@ -890,50 +1018,24 @@ extern "C" int b2i_plan_create(const b2i_chain_t* chain, int in_channels, b2i_pl
     if (op.kind == B2I_OP_LUT) memcpy(e.lut, op.lut, 256);
     el.push_back(e);
   }
-  // greedy segmentation: extend the segment while the tile kernel can still absorb it
-  size_t i = 0;
-  int c = in_channels;
-  while (i < el.size()) {
-    Segment best;
-    size_t best_end = i;
-    bool have = false;
-    for (size_t end = i + 1; end <= el.size(); ++end) {
-      std::vector<Elem> sub(el.begin() + i, el.begin() + end);
-      bool stencil = false;
-      for (const Elem& e : sub) stencil = stencil || e.kind == B2I_OP_STENCIL || e.kind == B2I_OP_SOBEL;
-      Segment seg;
-      bool ok = false;
-      if (!stencil) ok = build_pointwise_segment(sub, c, seg);
-      if (!ok) ok = build_tile_segment(sub, c, seg) == B2I_OK;
-      if (ok) {
-        TileParams P;  // also has to fit in shared memory at the smallest tile height
-        if (!seg.pointwise) {
-          layout(seg, 8, P);
-          ok = P.smem_bytes <= 227 * 1024;
-        }
-      }
-      if (!ok) break;
-      best = seg;
-      best_end = end;
-      have = true;
-    }
-    if (!have) {
-      delete plan;
-      B2I_FAIL(B2I_ERR_UNSUPPORTED, "op %zu of the chain cannot be scheduled on the GPU", i);
-    }
-    c = best.cout;
-    plan->segs.push_back(best);
-    i = best_end;
+  if (segment_chain(el, in_channels, false, plan->segs) != B2I_OK) {
+    delete plan;
+    B2I_FAIL(B2I_ERR_UNSUPPORTED, "the chain cannot be scheduled on the GPU");
   }
+  if (segment_chain(el, in_channels, true, plan->segs_split) != B2I_OK ||
+      plan->segs_split.size() == plan->segs.size())
+    plan->segs_split.clear();
   plan->info.cin = in_channels;
   plan->info.cout = cout;
   plan->info.halo = plan->halo;
-  plan->info.n_segments = (int)plan->segs.size();
-  for (size_t s = 0; s < plan->segs.size() && s < B2I_MAX_OPS; ++s) {
-    plan->info.seg_pointwise[s] = plan->segs[s].pointwise;
-    plan->info.seg_halo[s] = plan->segs[s].halo;
-    plan->info.seg_phases[s] = (int)plan->segs[s].phases.size();
-    plan->info.seg_cout[s] = plan->segs[s].cout;
+  // the cut with more segments is the one reported: callers size their tmp images by it
+  const std::vector<Segment>& rep = plan->segs_split.empty() ? plan->segs : plan->segs_split;
+  plan->info.n_segments = (int)rep.size();
+  for (size_t s = 0; s < rep.size() && s < B2I_MAX_OPS; ++s) {
+    plan->info.seg_pointwise[s] = rep[s].pointwise;
+    plan->info.seg_halo[s] = rep[s].halo;
+    plan->info.seg_phases[s] = (int)rep[s].phases.size();
+    plan->info.seg_cout[s] = rep[s].cout;
   }
   *out = plan;
   return B2I_OK;
@@ -963,7 +1065,17 @@ extern "C" int b2i_cuda_run(b2i_plan_t* plan, const b2i_launch_t* Lp) {
                 "bad geometry %dx%d rows [%d,%d)", L.W, L.H, L.y0, L.y1);
   if (L.y0 == L.y1) return B2I_OK;
   plan->info.last_launches = 0;
-  const int n = (int)plan->segs.size();
+  // the split cut only where the sweep kernels can take it: 8-pixel widths, TMA-encodable views
+  // and tmp images; anything else runs the fused cut on the tile kernel
+  auto tma_ok = [](const b2i_view_t& v) { return v.ptr && !(v.ptr & 15) && !(v.pitch & 15); };
+  const bool use_split = !plan->segs_split.empty() && !(L.flags & (B2I_LAUNCH_NO_TMA | B2I_LAUNCH_NAIVE)) &&
+                         !(L.W & 7) && L.W >= 16 && L.H >= 8 && tma_ok(L.src) && tma_ok(L.dst) &&
+                         tma_ok(L.tmp[0]) && (plan->segs_split.size() < 3 || tma_ok(L.tmp[1])) &&
+                         L.tmp[0].pitch >= (int64_t)L.W * 3 && !L.done_flag && tensor_map_encoder() &&
+                         !env_int("B200IMG_NO_SWEEP", 0) && !env_int("B200IMG_NO_TMA", 0) &&
+                         !env_int("B200IMG_NO_SPLIT", 0);
+  const std::vector<Segment>& segs = use_split ? plan->segs_split : plan->segs;
+  const int n = (int)segs.size();
   // Degenerate images (narrower or shorter than a border fold can reach) and explicit requests
   // go to the reference-style kernels.
   const bool tiny = plan->halo > 0 && (L.W <= 16 || L.H <= 16);
@@ -983,10 +1095,10 @@ extern "C" int b2i_cuda_run(b2i_plan_t* plan, const b2i_launch_t* Lp) {
   // Multi-segment plans over-compute: segment s produces the rows later segments still read
   // (communication-avoiding), so no synchronisation is needed inside one call.
   std::vector<int> rem(n + 1, 0);
-  for (int s = n - 1; s >= 0; --s) rem[s] = rem[s + 1] + plan->segs[s].halo;
+  for (int s = n - 1; s >= 0; --s) rem[s] = rem[s + 1] + segs[s].halo;
   b2i_view_t cur = L.src;
   for (int s = 0; s < n; ++s) {
-    const Segment& seg = plan->segs[s];
+    const Segment& seg = segs[s];
     const bool last = s == n - 1;
     const int ya = last ? L.y0 : std::max(0, L.y0 - rem[s + 1]);
     const int yb = last ? L.y1 : std::min(L.H, L.y1 + rem[s + 1]);

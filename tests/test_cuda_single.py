@@ -99,6 +99,20 @@ def test_tile_heights(tile_h):
     _check("gauss5,sobel", 1024, 333, tile_h=tile_h)
 
 
+@pytest.mark.parametrize("border", ["reflect101", "replicate", "zero"])
+@pytest.mark.parametrize("chain", ["gauss5", "gauss3", "sobel", "gauss5,sobel", "sobel,invert,gauss3"])
+def test_sweep_kernels_strip_and_segment_edges(chain, border):
+    """sweep5.cu / sweep_sobel.cu: widths around the 240-pixel strip, heights around the TMA box and
+    segment heights, every border rule that reaches them."""
+    from mpi_cuda_imagemanipulation_b200.ops.cuda import Plan
+    ch = ",".join(f"{op}@{border}" if op != "invert" else op for op in chain.split(","))
+    for W, H in [(32, 17), (240, 9), (496, 21), (256, 43), (480, 64), (976, 18), (960, 101), (1920, 19), (248, 30)]:
+        _check(ch, W, H, seed=W + H)
+    p = Plan(ch, 3)
+    p.run(torch.from_numpy(b2.synth_image(1024, 256)).cuda())
+    assert p.info()["tile_h"] < 0, p.info()     # negative: rows per sweep segment, i.e. a sweep kernel ran
+
+
 def test_plain_loaders_match_tma():
     for chain in ("kernel_cu", "kern_cpp", "gauss5,sobel"):
         _check(chain, 1024, 256, no_tma=True)
