@@ -171,10 +171,24 @@ class DistRuntime:
         torch.cuda.synchronize()
         return out
 
-    def _root_launch(self, no_tma=False) -> Launch:
+    def _attach_tmp(self, L: Launch, plan, W: int, H: int):
+        """Per-rank scratch images for plans of several segments (rows of the band plus its halo)."""
+        if plan is None or plan.n_segments <= 1 or L.y1 <= L.y0:
+            return
+        ra, rb = max(0, L.y0 - plan.halo), min(H, L.y1 + plan.halo)
+        pitch = (W * 3 + 15) // 16 * 16
+        need = pitch * (rb - ra)
+        if getattr(self, "_tmp", None) is None or self._tmp[0].numel() < need:
+            self._tmp = [torch.empty(need, dtype=torch.uint8, device=f"cuda:{torch.cuda.current_device()}")
+                         for _ in range(2)]
+        for k in range(2):
+            L.tmp[k] = View(self._tmp[k].data_ptr(), pitch, ra, rb)
+
+    def _root_launch(self, no_tma=False, plan=None) -> Launch:
         g = self.geom
         L = Launch()
         L.W, L.H, L.y0, L.y1 = g["W"], g["H"], self.y0, self.y1
+        self._attach_tmp(L, plan, g["W"], g["H"])
         L.src = View(self.src.ptrs[self.root], g["sp"], 0, g["H"])    # peer loads  = the scatter
         L.dst = View(self.dst.ptrs[self.root], g["dp"], 0, g["H"])    # peer stores = the gather
         L.counters = self.words.local + W_COUNTERS
@@ -186,7 +200,7 @@ class DistRuntime:
     def run_root(self, plan, steps: int = 1, no_tma: bool = False):
         """`steps` times: every rank produces its band of chain(root image) into the root's output.
         On the root, each step ends with a device-side wait for the other ranks' done flags."""
-        L = self._root_launch(no_tma)
+        L = self._root_launch(no_tma, plan)
         n_wait, flags = 0, (C.c_uint64 * _lib.B2I_MAX_GPUS)()
         if self.rank == self.root:
             for r in range(self.world):
@@ -247,11 +261,12 @@ class DistRuntime:
                                     self.stream()))
         self.barrier()
 
-    def _resident_launch(self, inb: int, halo: int, no_tma=False) -> Launch:
+    def _resident_launch(self, inb: int, halo: int, no_tma=False, plan=None) -> Launch:
         g = self.rgeom
         outb = inb ^ 1
         L = Launch()
         L.W, L.H, L.y0, L.y1 = g["W"], g["H"], self.y0, self.y1
+        self._attach_tmp(L, plan, g["W"], g["H"])
         va, vb = max(0, self.y0 - G), min(g["H"], self.y1 + G)
         L.src = View(self.band[inb].local + g["bp"] * (va - (self.y0 - G)), g["bp"], va, vb)
         L.dst = View(self.band[outb].local + g["bp"] * G, g["bp"], self.y0, self.y1)
@@ -278,7 +293,7 @@ class DistRuntime:
         halo = plan.halo
         if halo > G:
             raise ValueError(f"resident passes support a halo of at most {G} rows per pass")
-        even, odd = self._resident_launch(0, halo, no_tma), self._resident_launch(1, halo, no_tma)
+        even, odd = self._resident_launch(0, halo, no_tma, plan), self._resident_launch(1, halo, no_tma, plan)
         if self.y1 > self.y0:
             check(lib.b2i_cuda_run_resident_steps(plan.handle, C.byref(even), C.byref(odd), passes, self.epoch))
         self.epoch += passes + 1

@@ -22,8 +22,6 @@ def main():
     for chain, W, H in cases:
         img = b2.synth_image(W, H, 3, seed=W + H)
         plan = Plan(chain, 3)
-        if plan.n_segments > 1:
-            continue  # multi-segment plans need per-rank tmp images: covered by the in-process runtime
         rt.setup_root(W, H, 3, plan.cout)
         rt.load_root(img if rank == 0 else None)
         for no_tma in (False, True):
