@@ -129,6 +129,11 @@ struct b2i_ctx {
   uint32_t epoch = 0;
   bool peer_ok = true;
   double root_share = 0;  // ROOT mode: fraction of the rows the root GPU keeps (0 = equal bands)
+  // replicated output (b2i_ctx_set_replicated): one copy of the result per physical GPU behind one
+  // NVLS multicast address
+  bool replicated = false;
+  b2i_mcast_t* rep = nullptr;
+  std::vector<int> rep_devs;  // distinct physical devices, in order of first use
 };
 
 namespace {
@@ -162,6 +167,7 @@ extern "C" void b2i_ctx_destroy(b2i_ctx* c) {
     if (d.ev_stop) cudaEventDestroy(d.ev_stop);
     if (d.stream) cudaStreamDestroy(d.stream);
   }
+  if (c->rep) b2i_mcast_destroy(c->rep);
   if (c->n > 0) {
     cudaSetDevice(c->devs[c->root].id);
     if (c->root_src) cudaFree(c->root_src);
@@ -245,6 +251,15 @@ extern "C" int b2i_ctx_load_root(b2i_ctx* c, const uint8_t* src, int W, int H, i
   c->dst_pitch = align16((size_t)W * out_c);
   B2I_TRY(ensure(&c->root_src, &c->root_src_bytes, c->src_pitch * H));
   B2I_TRY(ensure(&c->root_dst, &c->root_dst_bytes, c->dst_pitch * H));
+  if (c->replicated && (!c->rep || b2i_mcast_bytes(c->rep) < c->dst_pitch * H)) {
+    if (c->rep) b2i_mcast_destroy(c->rep);
+    c->rep = nullptr;
+    c->rep_devs.clear();
+    for (const Dev& d : c->devs)
+      if (std::find(c->rep_devs.begin(), c->rep_devs.end(), d.id) == c->rep_devs.end()) c->rep_devs.push_back(d.id);
+    B2I_TRY(b2i_mcast_create((int)c->rep_devs.size(), c->rep_devs.data(), c->dst_pitch * H, &c->rep));
+    B2I_CUDA(cudaSetDevice(c->devs[c->root].id));
+  }
   B2I_CUDA(cudaMemcpy2DAsync(c->root_src, c->src_pitch, src, pitch, (size_t)W * C, H,
                              cudaMemcpyHostToDevice, r.stream));
   B2I_CUDA(cudaEventRecord(c->ev_src_ready, r.stream));
@@ -282,11 +297,47 @@ extern "C" int b2i_ctx_set_root_share(b2i_ctx* c, double share) {
 
 extern "C" int b2i_ctx_fetch_root(b2i_ctx* c, uint8_t* dst, size_t pitch) {
   B2I_CHECK_ARG(c && dst && c->root_dst, "nothing to fetch");
+  if (c->replicated && c->rep) return b2i_ctx_fetch_replica(c, c->root, dst, pitch);
   Dev& r = c->devs[c->root];
   B2I_CUDA(cudaSetDevice(r.id));
   B2I_CUDA(cudaMemcpy2DAsync(dst, pitch, c->root_dst, c->dst_pitch, (size_t)c->W * c->out_c, c->H,
                              cudaMemcpyDeviceToHost, r.stream));
   B2I_CUDA(cudaStreamSynchronize(r.stream));
+  return B2I_OK;
+}
+
+extern "C" int b2i_ctx_set_replicated(b2i_ctx* c, int on) {
+  B2I_CHECK_ARG(c, "null context");
+  if (on) {  // fail here, not at the next load, when the GPUs cannot do it
+    std::vector<int> devs;
+    for (const Dev& d : c->devs)
+      if (std::find(devs.begin(), devs.end(), d.id) == devs.end()) devs.push_back(d.id);
+    b2i_mcast_t* probe = nullptr;
+    B2I_TRY(b2i_mcast_create((int)devs.size(), devs.data(), 4096, &probe));
+    b2i_mcast_destroy(probe);
+    B2I_CUDA(cudaSetDevice(c->devs[c->root].id));
+  }
+  c->replicated = on != 0;
+  if (!on && c->rep) {
+    b2i_mcast_destroy(c->rep);
+    c->rep = nullptr;
+  }
+  return B2I_OK;
+}
+
+extern "C" int b2i_ctx_replicated(const b2i_ctx* c) {
+  if (!c || !c->replicated) return 0;
+  return c->rep && b2i_mcast_is_multicast(c->rep) ? 2 : c->rep ? 1 : (int)c->replicated;
+}
+
+extern "C" int b2i_ctx_fetch_replica(b2i_ctx* c, int gpu, uint8_t* dst, size_t pitch) {
+  B2I_CHECK_ARG(c && dst && c->rep && gpu >= 0 && gpu < c->n, "no replicated output to fetch");
+  Dev& d = c->devs[gpu];
+  const int k = (int)(std::find(c->rep_devs.begin(), c->rep_devs.end(), d.id) - c->rep_devs.begin());
+  B2I_CUDA(cudaSetDevice(d.id));
+  B2I_CUDA(cudaMemcpy2DAsync(dst, pitch, reinterpret_cast<const void*>(b2i_mcast_replica(c->rep, k)), c->dst_pitch,
+                             (size_t)c->W * c->out_c, c->H, cudaMemcpyDeviceToHost, d.stream));
+  B2I_CUDA(cudaStreamSynchronize(d.stream));
   return B2I_OK;
 }
 
@@ -333,12 +384,14 @@ extern "C" int b2i_ctx_run_root(b2i_ctx* c, b2i_plan_t* plan, int iters, int fla
       L.y1 = d.y1;
       L.src = {(uint64_t)c->root_src, (int64_t)c->src_pitch, 0, c->H};  // peer loads: the scatter
       L.dst = {(uint64_t)c->root_dst, (int64_t)c->dst_pitch, 0, c->H};  // peer stores: the gather
+      if (c->replicated && c->rep)  // one store per byte, replicated into every GPU by the switch
+        L.dst = {b2i_mcast_ptr(c->rep), (int64_t)c->dst_pitch, 0, c->H};
       if (info.n_segments > 1) {
         L.tmp[0] = {(uint64_t)d.tmp[0], (int64_t)c->W * 3, ra, rb};
         L.tmp[1] = {(uint64_t)d.tmp[1], (int64_t)c->W * 3, ra, rb};
       }
       L.stream = d.stream;
-      L.flags = flags;
+      L.flags = flags | (c->replicated && c->rep ? B2I_LAUNCH_DST_MCAST : 0);
       B2I_TRY(b2i_cuda_run(plan, &L));
     }
     B2I_CUDA(cudaEventRecord(d.ev_stop, d.stream));

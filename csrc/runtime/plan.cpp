@@ -475,10 +475,11 @@ int env_int(const char* name, int dflt) {
 // gray (+LUT) -> one 3x3 stencil on the gray plane (+LUT, +expand). Returns 1 if it launched,
 // 0 if the segment or the buffers do not qualify (the tile-chain kernel then runs it).
 int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
-              const b2i_view_t& src, const b2i_view_t& dst, int sms) {
+              const b2i_view_t& src, const b2i_view_t& dst, int sms, bool last) {
   if (seg.phases.size() != 2 || env_int("B200IMG_NO_SWEEP", 0) || (L.flags & B2I_LAUNCH_NO_TMA) ||
       env_int("B200IMG_NO_TMA", 0))
     return 0;
+  if (last && (L.flags & B2I_LAUNCH_DST_MCAST)) return 0;
   const PhaseDesc& g = seg.phases[0];
   const PhaseDesc& st = seg.phases[1];
   if ((g.type != PH_GRAY_REF && g.type != PH_GRAY_CV) || st.type != PH_STENCIL || st.ksize != 3 ||
@@ -619,6 +620,7 @@ int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0
   if (seg.phases.size() != 2 || env_int("B200IMG_NO_SWEEP", 0) || env_int("B200IMG_NO_SWEEP5", 0) ||
       (L.flags & B2I_LAUNCH_NO_TMA) || env_int("B200IMG_NO_TMA", 0))
     return 0;
+  if (last && (L.flags & B2I_LAUNCH_DST_MCAST)) return 0;
   const PhaseDesc& ph = seg.phases[0];
   const PhaseDesc& pv = seg.phases[1];
   if (ph.type != PH_SEPH || pv.type != PH_SEPV || seg.cin != 3 || seg.cout != 3 || pv.expand) return 0;
@@ -678,6 +680,7 @@ int try_sweep_sobel(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, i
   if (seg.phases.size() != 1 || env_int("B200IMG_NO_SWEEP", 0) || env_int("B200IMG_NO_SWEEP_SOBEL", 0) ||
       (L.flags & B2I_LAUNCH_NO_TMA) || env_int("B200IMG_NO_TMA", 0))
     return 0;
+  if (last && (L.flags & B2I_LAUNCH_DST_MCAST)) return 0;
   const PhaseDesc& ph = seg.phases[0];
   if (ph.type != PH_SOBEL || seg.cin != 3 || seg.cout != 3 || ph.expand || ph.border == B2I_BORDER_REF) return 0;
   if ((L.W & 7) || L.W < 16 || L.H < 8 || y1 - y0 < 1) return 0;
@@ -733,7 +736,7 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
     const int need_a = std::max(0, y0 - seg.halo), need_b = std::min(L.H, y1 + seg.halo);
     B2I_CHECK_ARG(src.y_begin <= need_a && src.y_end >= need_b && dst.y_begin <= y0 && dst.y_end >= y1,
                   "views do not cover the band [%d,%d) and its halo", y0, y1);
-    int sw = try_sweep(plan, seg, L, y0, y1, src, dst, sms);
+    int sw = try_sweep(plan, seg, L, y0, y1, src, dst, sms, last);
     if (sw == 0) sw = try_sweep5(plan, seg, L, y0, y1, src, dst, sms, first, last);
     if (sw == 0) sw = try_sweep_sobel(plan, seg, L, y0, y1, src, dst, sms, first, last);
     if (sw < 0) return B2I_ERR_CUDA;
@@ -851,7 +854,7 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
   memset(&up_map, 0, sizeof up_map);
   memset(&dn_map, 0, sizeof dn_map);
   const bool no_tma_load = no_tma || env_int("B200IMG_NO_TMA_LOAD", 0);
-  const bool no_tma_store = no_tma || env_int("B200IMG_NO_TMA_STORE", 0);
+  const bool no_tma_store = no_tma || env_int("B200IMG_NO_TMA_STORE", 0) || (last && (L.flags & B2I_LAUNCH_DST_MCAST));
   P.use_tma_load = !no_tma_load && encode_map(&src_map, P.src_ptr, P.src_pitch, (int64_t)L.W * seg.cin,
                                          P.src_y_end - P.src_y_begin, kPlaneW * seg.cin, P.raw_rows);
   P.use_tma_store = !no_tma_store && encode_map(&dst_map, P.dst_ptr, P.dst_pitch, (int64_t)L.W * seg.cout,

@@ -159,6 +159,9 @@ typedef struct b2i_view {
 
 #define B2I_LAUNCH_NO_TMA 1   /* force the plain ld/st tile loaders (debug, unaligned images) */
 #define B2I_LAUNCH_NAIVE 2    /* reference-style one-launch-per-op kernels (baseline / oracle) */
+#define B2I_LAUNCH_DST_MCAST 4 /* dst is an NVLS multicast address (b2i_mcast_ptr): result rows leave by
+                                  plain stores from registers / shared memory, which the switch
+                                  replicates into every GPU's copy; TMA stores are not used on it */
 
 /* One band launch: produce rows [y0, y1) of chain(image) into dst, reading src.
  * src must cover rows [y0-halo, y1+halo) clipped to the image (halo = b2i_plan_halo); when src
@@ -277,6 +280,28 @@ int b2i_ctx_run_direct(b2i_ctx_t* ctx, b2i_plan_t* plan, const uint8_t* src, int
 int b2i_ctx_run_cli(int gpus, int root, const b2i_chain_t* chain, const uint8_t* src, int W, int H,
                     int C, uint8_t* dst, int iters, int flags, int resident, double* kernel_ms,
                     double* total_ms, char* report, size_t report_len);
+
+/* Replicated output: ROOT mode ends with the whole result on EVERY GPU instead of on the root
+ * only. The last kernel of each GPU stores its band once, to an NVLS multicast address, and the
+ * NVSwitch writes all copies (one plain buffer stands in when the context has one physical GPU).
+ * Takes effect at the next b2i_ctx_load_root. Returns B2I_ERR_UNSUPPORTED without multicast. */
+int b2i_ctx_set_replicated(b2i_ctx_t* ctx, int on);
+/* 0 = off, 1 = on with a plain buffer (one physical GPU), 2 = on through an NVLS multicast object. */
+int b2i_ctx_replicated(const b2i_ctx_t* ctx);
+/* GPU `gpu`'s copy of the replicated output -> host. Synchronises. */
+int b2i_ctx_fetch_replica(b2i_ctx_t* ctx, int gpu, uint8_t* dst, size_t pitch);
+
+/* ---- NVLS multicast images (csrc/runtime/mcast.cpp); no counterpart in the reference ---------- */
+
+/* `bytes` on each of n distinct devices (cuMemCreate) bound to one multicast object
+ * (cuMulticastCreate / cuMulticastBindMem): a store to b2i_mcast_ptr lands in every replica. */
+typedef struct b2i_mcast b2i_mcast_t;
+int b2i_mcast_create(int n, const int* devices, size_t bytes, b2i_mcast_t** out);
+void b2i_mcast_destroy(b2i_mcast_t* m);
+uint64_t b2i_mcast_ptr(const b2i_mcast_t* m);             /* the multicast address (write-only use) */
+uint64_t b2i_mcast_replica(const b2i_mcast_t* m, int i);  /* device i's copy, an ordinary pointer */
+size_t b2i_mcast_bytes(const b2i_mcast_t* m);
+int b2i_mcast_is_multicast(const b2i_mcast_t* m);          /* 0: n == 1, a plain allocation */
 
 /* ---- multi-process plumbing (csrc/runtime/ipc.cu): one process per GPU, as under torchrun ---- */
 

@@ -114,7 +114,7 @@ def has(symbol: str) -> bool:
 
 
 # ---- CUDA path (present once the kernels are linked in) ----------------------------------------
-LAUNCH_NO_TMA, LAUNCH_NAIVE = 1, 2
+LAUNCH_NO_TMA, LAUNCH_NAIVE, LAUNCH_DST_MCAST = 1, 2, 4
 
 
 class View(C.Structure):
@@ -164,6 +164,15 @@ _sig("b2i_ctx_gpus", C.c_int, C.c_void_p)
 _sig("b2i_ctx_load_root", C.c_int, C.c_void_p, u8p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_int)
 _sig("b2i_ctx_set_root_share", C.c_int, C.c_void_p, C.c_double)
 _sig("b2i_ctx_fetch_root", C.c_int, C.c_void_p, u8p, C.c_size_t)
+_sig("b2i_ctx_set_replicated", C.c_int, C.c_void_p, C.c_int)
+_sig("b2i_ctx_replicated", C.c_int, C.c_void_p)
+_sig("b2i_ctx_fetch_replica", C.c_int, C.c_void_p, C.c_int, u8p, C.c_size_t)
+_sig("b2i_mcast_create", C.c_int, C.c_int, _P(C.c_int), C.c_size_t, _P(C.c_void_p))
+_sig("b2i_mcast_destroy", None, C.c_void_p)
+_sig("b2i_mcast_ptr", C.c_uint64, C.c_void_p)
+_sig("b2i_mcast_replica", C.c_uint64, C.c_void_p, C.c_int)
+_sig("b2i_mcast_bytes", C.c_size_t, C.c_void_p)
+_sig("b2i_mcast_is_multicast", C.c_int, C.c_void_p)
 _sig("b2i_ctx_run_root", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, _P(C.c_double),
      _P(C.c_double))
 _sig("b2i_ctx_run_resident", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,

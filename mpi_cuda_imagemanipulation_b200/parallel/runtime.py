@@ -58,7 +58,8 @@ class Runtime:
         return self._plans[key]
 
     def run(self, img: np.ndarray, chain, *, mode: str = "root", iters: int = 1, passes: int = 1,
-            sync: str = "events", no_tma: bool = False, root_share=None, **kw) -> np.ndarray:
+            sync: str = "events", no_tma: bool = False, root_share=None, replicate: bool = False,
+            **kw) -> np.ndarray:
         """Host image in, host image out.
 
         mode="root":     scatter/gather fused into the kernels through the root GPU's memory.
@@ -67,6 +68,11 @@ class Runtime:
         mode="resident": bands stay on their GPUs for ``passes`` applications of the chain,
                          halos pushed by the kernels; ``sync`` is "events" or "flags".
         mode="direct":   each GPU moves its band over its own PCIe link.
+
+        replicate=True (mode="root"): the result ends on every GPU, not on the root only — each
+        kernel stores its band once to an NVLS multicast address and the NVSwitch writes all
+        copies. ``self.replicas`` then holds every GPU's copy (host arrays), ``self.nvls`` says
+        whether a multicast object (True) or the one-GPU stand-in (False) carried it.
         """
         img = np.ascontiguousarray(img, dtype=np.uint8)
         H, W, Cn = image_geometry(img)
@@ -80,6 +86,9 @@ class Runtime:
             check(lib.b2i_ctx_run_direct(self._c, plan.handle, img.ctypes.data, W, H, Cn, W * Cn,
                                          out.ctypes.data, W * oc, flags, C.byref(ms)))
         else:
+            if replicate and mode != "root":
+                raise ValueError("replicate=True needs mode='root'")
+            check(lib.b2i_ctx_set_replicated(self._c, int(bool(replicate))))
             share = 0.0 if root_share in (None, "auto") else float(root_share)
             check(lib.b2i_ctx_set_root_share(self._c, share if mode == "root" else 0.0))
             check(lib.b2i_ctx_load_root(self._c, img.ctypes.data, W, H, Cn, W * Cn, oc))
@@ -103,6 +112,14 @@ class Runtime:
             else:
                 raise ValueError(f"unknown mode {mode!r}")
             check(lib.b2i_ctx_fetch_root(self._c, out.ctypes.data, W * oc))
+            self.replicas = None
+            if replicate:
+                self.nvls = lib.b2i_ctx_replicated(self._c) == 2
+                self.replicas = []
+                for g in range(self.gpus):
+                    r = np.empty((H, W, oc), np.uint8)
+                    check(lib.b2i_ctx_fetch_replica(self._c, g, r.ctypes.data, W * oc))
+                    self.replicas.append(r)
         self.last_ms = ms.value
         self.last_per_gpu_ms = list(per)
         return out if img.ndim == 3 or oc == 3 else out[:, :, 0]

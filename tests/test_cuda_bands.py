@@ -68,6 +68,21 @@ def test_direct_mode(n):
             assert np.array_equal(rt.run(img, chain, mode="direct"), b2.host_run(chain, img))
 
 
+@pytest.mark.parametrize("chain", ["kernel_cu", "gauss5,sobel", "invert", "gauss5"])
+def test_replicated_output_plain_store_path(chain):
+    """replicate=True: the last kernel leaves by plain stores to the (here: stand-in) multicast
+    address. On one physical GPU all virtual GPUs share one copy; tests/test_multigpu.py checks
+    the NVLS object on real peers."""
+    from mpi_cuda_imagemanipulation_b200.parallel import Runtime
+    img = b2.synth_image(1024, 403, seed=4)
+    want = b2.host_run(chain, img)
+    with Runtime(gpus=4) as rt:
+        got = rt.run(img, chain, mode="root", replicate=True)
+        assert np.array_equal(got, want)
+        assert len(rt.replicas) == 4 and all(np.array_equal(r, want) for r in rt.replicas)
+        assert np.array_equal(rt.run(img, chain, mode="root"), want)      # and back to root-only output
+
+
 def test_topology_report():
     from mpi_cuda_imagemanipulation_b200.parallel import topology
     t = topology()

@@ -38,3 +38,24 @@ def test_in_process_runtime_on_real_peers():
         assert np.array_equal(rt.run(img, "gauss5", mode="resident", passes=3), want)
         assert np.array_equal(rt.run(img, "gauss5", mode="resident", passes=3, sync="flags"), want)
         assert np.array_equal(rt.run(img, "kernel_cu", mode="direct"), b2.host_run("kernel_cu", img))
+
+
+def test_nvls_multicast_replicated_output():
+    """Every GPU ends up with the whole result through ONE store per byte (NVLS multicast)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import numpy as np
+    import mpi_cuda_imagemanipulation_b200 as b2
+    from mpi_cuda_imagemanipulation_b200.parallel import Runtime, topology
+    n = min(torch.cuda.device_count(), 8)
+    if not all(d.get("multicast") == 1 for d in topology()["devices"][:n]):
+        pytest.skip("no multicast support on this box")
+    img = b2.synth_image(2048, 1030, seed=6)
+    with Runtime(gpus=n) as rt:
+        for chain in ("kernel_cu", "gauss5,sobel", "gray"):
+            want = b2.host_run(chain, img)
+            got = rt.run(img, chain, mode="root", replicate=True)
+            assert rt.nvls, "expected a multicast object on real peers"
+            assert np.array_equal(got, want), chain
+            for g, r in enumerate(rt.replicas):
+                assert np.array_equal(r, want), (chain, g)
