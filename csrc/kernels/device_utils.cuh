@@ -85,6 +85,15 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
+// ---- NVLS multicast stores ------------------------------------------------------------------------
+// 8 bytes to a multicast address (b2i_mcast_ptr): the NVSwitch replicates the store into every
+// bound GPU's copy. On an ordinary address it is an ordinary store (same SASS: STG.E.64).
+__device__ __forceinline__ void st_mc_v2(uint64_t addr, uint32_t a, uint32_t b) {
+  asm volatile("multimem.st.global.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(__uint_as_float(a)),
+               "f"(__uint_as_float(b))
+               : "memory");
+}
+
 // ---- cross-GPU flags (peer-mapped or IPC-mapped global memory) ---------------------------------
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");

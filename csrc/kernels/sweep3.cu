@@ -80,7 +80,9 @@ __device__ __forceinline__ void gray8(const uint8_t* s, const GrayRefCoef& gk, i
   }
 }
 
-template <int GRAY, bool LUT0>
+// PLAIN: result rows leave by 8-byte stores from registers (NVLS multicast output) instead of the
+// staging buffer + TMA store; a separate instantiation, so the single-GPU kernel pays nothing.
+template <int GRAY, bool LUT0, bool PLAIN>
 __global__ void __launch_bounds__(kWarps * 32, kSweepCtasPerSm)
 sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUtensorMap src_map,
               const __grid_constant__ CUtensorMap dst_map) {
@@ -97,7 +99,7 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
     for (int i = 0; i < kWarps * NST; ++i) mbar_init(&bars[i], 1);
     fence_mbar_init();
     tma_prefetch_desc(&src_map);
-    tma_prefetch_desc(&dst_map);
+    if (!PLAIN) tma_prefetch_desc(&dst_map);
   }
   __syncthreads();  // the only block-wide barrier of the kernel
 
@@ -238,7 +240,19 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
           r0 = lut4s(lut1, r0);
           r1 = lut4s(lut1, r1);
         }
-        {
+        if constexpr (PLAIN) {  // NVLS: one store per byte, the switch writes every GPU's copy
+          if (!halo_lane && !beyond) {
+            const uint64_t g = P.plain_dst_ptr + (int64_t)(y - 1 - P.y0) * P.plain_dst_pitch +
+                               (int64_t)xs * (P.expand ? 3 : 1) + (lane - 1) * (P.expand ? 24 : 8);
+            if (P.expand) {
+              st_mc_v2(g, __byte_perm(r0, 0, 0x1000), __byte_perm(r0, 0, 0x2211));
+              st_mc_v2(g + 8, __byte_perm(r0, 0, 0x3332), __byte_perm(r1, 0, 0x1000));
+              st_mc_v2(g + 16, __byte_perm(r1, 0, 0x2211), __byte_perm(r1, 0, 0x3332));
+            } else {
+              st_mc_v2(g, r0, r1);
+            }
+          }
+        } else {
           // halo lanes (0, 31) store into a per-warp dummy slot: no divergent branch around the stores
           uint8_t* d = halo_lane ? dummy : out_ring + ob * P.out_buf_bytes + er * out_pitch + (lane - 1) * (P.expand ? 24 : 8);
           if (P.expand) {  // kernel.cu:210 in registers: 8 gray -> 24 bytes
@@ -250,7 +264,7 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
             *reinterpret_cast<uint2*>(d) = make_uint2(r0, r1);
           }
         }
-        if (er == 2 || u == steps - 1) {  // a box of finished rows leaves by TMA
+        if (!PLAIN && (er == 2 || u == steps - 1)) {  // a box of finished rows leaves by TMA
           const int ec = (u - 2) / CH;
           fence_proxy_async_smem();
           __syncwarp();
@@ -291,12 +305,12 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
 
 cudaError_t launch_sweep3(const SweepParams& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
                           int grid, cudaStream_t stream) {
-  static bool configured[64][4] = {{false}};
+  static bool configured[64][8] = {{false}};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   const int smem = P.warp_smem * kSweepWarps;
-  const int variant = (P.gray == 1 ? 0 : 2) + (P.has_lut0 ? 1 : 0);
+  const int variant = (P.gray == 1 ? 0 : 2) + (P.has_lut0 ? 1 : 0) + (P.plain_dst_ptr ? 4 : 0);
   auto launch = [&](auto kern) -> cudaError_t {
     if (dev < 64 && !configured[dev][variant]) {
       cudaError_t e2 = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
@@ -307,10 +321,14 @@ cudaError_t launch_sweep3(const SweepParams& P, const CUtensorMap& src_map, cons
     return cudaGetLastError();
   };
   switch (variant) {
-    case 0: return launch(sweep3_kernel<1, false>);
-    case 1: return launch(sweep3_kernel<1, true>);
-    case 2: return launch(sweep3_kernel<2, false>);
-    default: return launch(sweep3_kernel<2, true>);
+    case 0: return launch(sweep3_kernel<1, false, false>);
+    case 1: return launch(sweep3_kernel<1, true, false>);
+    case 2: return launch(sweep3_kernel<2, false, false>);
+    case 3: return launch(sweep3_kernel<2, true, false>);
+    case 4: return launch(sweep3_kernel<1, false, true>);
+    case 5: return launch(sweep3_kernel<1, true, true>);
+    case 6: return launch(sweep3_kernel<2, false, true>);
+    default: return launch(sweep3_kernel<2, true, true>);
   }
 }
 

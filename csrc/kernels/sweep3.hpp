@@ -24,6 +24,10 @@ struct SweepParams {
   int32_t border, shift, bias, expand;
   int32_t warp_smem;          // bytes of dynamic shared memory per warp
   int32_t in_stage_bytes, out_buf_bytes;  // 128-byte aligned sizes of one input stage / one staging buffer
+  // replicated output: result rows leave by 8-byte stores from registers to this address (row y0
+  // of an NVLS multicast image) instead of the staging buffer + TMA store; 0 = off
+  uint64_t plain_dst_ptr;
+  int64_t plain_dst_pitch;
   uint32_t wpk[3];            // 3x3 weights, one dp4a operand per stencil row
   uint8_t lut0[256], lut1[256];
 };

@@ -68,6 +68,9 @@ __device__ __forceinline__ void vacc(uint32_t (&acc)[12], const uint32_t (&h)[12
   for (int i = 0; i < 12; ++i) acc[i] = INIT ? h[i] * w : acc[i] + h[i] * w;
 }
 
+// MG: the multi-GPU hooks (neighbour flags, halo pushes, NVLS multicast output) are compiled in.
+// The single-GPU instantiation carries none of them.
+template <bool MG>
 __global__ void __launch_bounds__(kS5Warps * 32, kS5CtasPerSm)
 sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CUtensorMap src_map,
               const __grid_constant__ CUtensorMap dst_map) {
@@ -81,7 +84,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
     for (int i = 0; i < kS5Warps * NST; ++i) mbar_init(&bars[i], 1);
     fence_mbar_init();
     tma_prefetch_desc(&src_map);
-    tma_prefetch_desc(&dst_map);
+    if (!(MG && P.plain_dst_ptr)) tma_prefetch_desc(&dst_map);
   }
   __syncthreads();  // the only block-wide barrier of the kernel
 
@@ -115,15 +118,15 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
     const int xw_in = (xs * 3 - 32) >> 2, xw_out = (xs * 3) >> 2;
     // A task that reads ghost rows, or writes the neighbour's, first sees the neighbour's flag of
     // the previous pass: its rows have landed here and it has finished reading what we overwrite.
-    const bool sig_up = P.signal_up_flag && ya < P.y0 + P.push_rows;
-    const bool sig_dn = P.signal_dn_flag && yb > P.y1 - P.push_rows;
+    const bool sig_up = MG && P.signal_up_flag && ya < P.y0 + P.push_rows;
+    const bool sig_dn = MG && P.signal_dn_flag && yb > P.y1 - P.push_rows;
     if (lane == 0) {
-      if (P.wait_up_flag && (ya - 2 < P.y0 || sig_up)) {
+      if (MG && P.wait_up_flag && (ya - 2 < P.y0 || sig_up)) {
         if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_up_flag), P.wait_epoch, P.timeout_ns))
           atomicExch(reinterpret_cast<uint32_t*>(P.status), 1u);
         asm volatile("fence.proxy.async;" ::: "memory");
       }
-      if (P.wait_dn_flag && (yb + 2 > P.y1 || sig_dn)) {
+      if (MG && P.wait_dn_flag && (yb + 2 > P.y1 || sig_dn)) {
         if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_dn_flag), P.wait_epoch, P.timeout_ns))
           atomicExch(reinterpret_cast<uint32_t*>(P.status), 2u);
         asm volatile("fence.proxy.async;" ::: "memory");
@@ -230,12 +233,21 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
 #pragma unroll
           for (int m = 0; m < 6; ++m) r[m] = lut4q(lut1, r[m]);
         }
-        uint2* d = reinterpret_cast<uint2*>(halo_lane ? dummy
-                                                      : out_ring + ob * P.out_buf_bytes + er * kS5OutBytes + (lane - 1) * 24);
-        d[0] = make_uint2(r[0], r[1]);
-        d[1] = make_uint2(r[2], r[3]);
-        d[2] = make_uint2(r[4], r[5]);
-        if (P.push_rows) {  // halo rows also go straight from registers into the neighbours' ghost rows
+        if (MG && P.plain_dst_ptr) {  // NVLS: one store per byte, the switch writes every GPU's copy
+          if (!halo_lane && !beyond) {
+            const uint64_t g = P.plain_dst_ptr + (int64_t)(y - 2 - P.y0) * P.plain_dst_pitch + (int64_t)xs * 3 + (lane - 1) * 24;
+            st_mc_v2(g, r[0], r[1]);
+            st_mc_v2(g + 8, r[2], r[3]);
+            st_mc_v2(g + 16, r[4], r[5]);
+          }
+        } else {
+          uint2* d = reinterpret_cast<uint2*>(halo_lane ? dummy
+                                                        : out_ring + ob * P.out_buf_bytes + er * kS5OutBytes + (lane - 1) * 24);
+          d[0] = make_uint2(r[0], r[1]);
+          d[1] = make_uint2(r[2], r[3]);
+          d[2] = make_uint2(r[4], r[5]);
+        }
+        if (MG && P.push_rows) {  // halo rows also go straight from registers into the neighbours' ghost rows
           const int oy = y - 2;
           if (!halo_lane && !beyond) {
             const int64_t col = (int64_t)xs * 3 + (lane - 1) * 24;
@@ -254,7 +266,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
             }
           }
         }
-        if (er == 4 || u == steps - 1) {  // a box of finished rows leaves by TMA
+        if (!(MG && P.plain_dst_ptr) && (er == 4 || u == steps - 1)) {  // a box of finished rows leaves by TMA
           const int ec = (u - 4) / CH;
           fence_proxy_async_smem();
           __syncwarp();
@@ -310,16 +322,19 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
 
 cudaError_t launch_sweep5(const Sweep5Params& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
                           int grid, cudaStream_t stream) {
-  static bool configured[64] = {false};
+  static bool configured[64][2] = {{false}};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
-  if (dev < 64 && !configured[dev]) {
-    e = cudaFuncSetAttribute(sweep5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  const bool mg = P.push_rows || P.wait_up_flag || P.wait_dn_flag || P.signal_up_flag || P.signal_dn_flag ||
+                  P.plain_dst_ptr;
+  auto kern = mg ? sweep5_kernel<true> : sweep5_kernel<false>;
+  if (dev < 64 && !configured[dev][mg]) {
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     if (e != cudaSuccess) return e;
-    configured[dev] = true;
+    configured[dev][mg] = true;
   }
-  sweep5_kernel<<<grid, kS5Warps * 32, P.warp_smem * kS5Warps, stream>>>(P, src_map, dst_map);
+  kern<<<grid, kS5Warps * 32, P.warp_smem * kS5Warps, stream>>>(P, src_map, dst_map);
   return cudaGetLastError();
 }
 }  // namespace b2i

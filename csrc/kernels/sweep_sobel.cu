@@ -46,6 +46,9 @@ __device__ __forceinline__ uint32_t od(uint32_t w) { return __byte_perm(w, 0u, 0
 // |v - 1024| + 1024 per lane, for lanes in [4, 2044]
 __device__ __forceinline__ uint32_t abs_biased(uint32_t v) { return __vmaxu2(v, 0x08000800u - v); }
 
+// MG: the multi-GPU hooks (neighbour flags, halo pushes, NVLS multicast output) are compiled in.
+// The single-GPU instantiation carries none of them.
+template <bool MG>
 __global__ void __launch_bounds__(kSSWarps * 32, kSSCtasPerSm)
 sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_constant__ CUtensorMap src_map,
                    const __grid_constant__ CUtensorMap dst_map) {
@@ -59,7 +62,7 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
     for (int i = 0; i < kSSWarps * NST; ++i) mbar_init(&bars[i], 1);
     fence_mbar_init();
     tma_prefetch_desc(&src_map);
-    tma_prefetch_desc(&dst_map);
+    if (!(MG && P.plain_dst_ptr)) tma_prefetch_desc(&dst_map);
   }
   __syncthreads();  // the only block-wide barrier of the kernel
 
@@ -82,16 +85,16 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
     const int xs = strip * kSSStrip;
     const int x0 = xs - 8 + lane * 8;                // first pixel this lane holds
     const int xw_in = (xs * 3 - 32) >> 2, xw_out = (xs * 3) >> 2;
-    const bool sig_up = P.signal_up_flag && ya < P.y0 + P.push_rows;
-    const bool sig_dn = P.signal_dn_flag && yb > P.y1 - P.push_rows;
+    const bool sig_up = MG && P.signal_up_flag && ya < P.y0 + P.push_rows;
+    const bool sig_dn = MG && P.signal_dn_flag && yb > P.y1 - P.push_rows;
     if (lane == 0) {
       // a task that reads ghost rows, or writes the neighbour's, first sees the neighbour's flag
-      if (P.wait_up_flag && (ya - 1 < P.y0 || sig_up)) {
+      if (MG && P.wait_up_flag && (ya - 1 < P.y0 || sig_up)) {
         if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_up_flag), P.wait_epoch, P.timeout_ns))
           atomicExch(reinterpret_cast<uint32_t*>(P.status), 1u);
         asm volatile("fence.proxy.async;" ::: "memory");
       }
-      if (P.wait_dn_flag && (yb + 1 > P.y1 || sig_dn)) {
+      if (MG && P.wait_dn_flag && (yb + 1 > P.y1 || sig_dn)) {
         if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_dn_flag), P.wait_epoch, P.timeout_ns))
           atomicExch(reinterpret_cast<uint32_t*>(P.status), 2u);
         asm volatile("fence.proxy.async;" ::: "memory");
@@ -190,12 +193,21 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
 #pragma unroll
           for (int m = 0; m < 6; ++m) r[m] = lut4s(lut1, r[m]);
         }
-        uint2* d = reinterpret_cast<uint2*>(halo_lane ? dummy
-                                                      : out_ring + ob * P.out_buf_bytes + er * kSSOutBytes + (lane - 1) * 24);
-        d[0] = make_uint2(r[0], r[1]);
-        d[1] = make_uint2(r[2], r[3]);
-        d[2] = make_uint2(r[4], r[5]);
-        if (P.push_rows) {  // halo rows also go straight from registers into the neighbours' ghost rows
+        if (MG && P.plain_dst_ptr) {  // NVLS: one store per byte, the switch writes every GPU's copy
+          if (!halo_lane && !beyond) {
+            const uint64_t g = P.plain_dst_ptr + (int64_t)(y - 1 - P.y0) * P.plain_dst_pitch + (int64_t)xs * 3 + (lane - 1) * 24;
+            st_mc_v2(g, r[0], r[1]);
+            st_mc_v2(g + 8, r[2], r[3]);
+            st_mc_v2(g + 16, r[4], r[5]);
+          }
+        } else {
+          uint2* d = reinterpret_cast<uint2*>(halo_lane ? dummy
+                                                        : out_ring + ob * P.out_buf_bytes + er * kSSOutBytes + (lane - 1) * 24);
+          d[0] = make_uint2(r[0], r[1]);
+          d[1] = make_uint2(r[2], r[3]);
+          d[2] = make_uint2(r[4], r[5]);
+        }
+        if (MG && P.push_rows) {  // halo rows also go straight from registers into the neighbours' ghost rows
           const int oy = y - 1;
           if (!halo_lane && !beyond) {
             const int64_t col = (int64_t)xs * 3 + (lane - 1) * 24;
@@ -214,7 +226,7 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
             }
           }
         }
-        if (er == CH - 1 || u == steps - 1) {  // a box of finished rows leaves by TMA
+        if (!(MG && P.plain_dst_ptr) && (er == CH - 1 || u == steps - 1)) {  // a box of finished rows leaves by TMA
           const int ec = (u - 2) / CH;
           fence_proxy_async_smem();
           __syncwarp();
@@ -272,16 +284,19 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
 
 cudaError_t launch_sweep_sobel(const SweepSobelParams& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
                                int grid, cudaStream_t stream) {
-  static bool configured[64] = {false};
+  static bool configured[64][2] = {{false}};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
-  if (dev < 64 && !configured[dev]) {
-    e = cudaFuncSetAttribute(sweep_sobel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  const bool mg = P.push_rows || P.wait_up_flag || P.wait_dn_flag || P.signal_up_flag || P.signal_dn_flag ||
+                  P.plain_dst_ptr;
+  auto kern = mg ? sweep_sobel_kernel<true> : sweep_sobel_kernel<false>;
+  if (dev < 64 && !configured[dev][mg]) {
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     if (e != cudaSuccess) return e;
-    configured[dev] = true;
+    configured[dev][mg] = true;
   }
-  sweep_sobel_kernel<<<grid, kSSWarps * 32, P.warp_smem * kSSWarps, stream>>>(P, src_map, dst_map);
+  kern<<<grid, kSSWarps * 32, P.warp_smem * kSSWarps, stream>>>(P, src_map, dst_map);
   return cudaGetLastError();
 }
 }  // namespace b2i

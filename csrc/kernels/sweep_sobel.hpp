@@ -27,6 +27,10 @@ struct SweepSobelParams {
   uint64_t push_up_ptr, push_dn_ptr;
   uint64_t wait_up_flag, wait_dn_flag, signal_up_flag, signal_dn_flag;
   uint64_t counters, status, timeout_ns;
+  // replicated output: result rows leave by 8-byte stores from registers to this address (row y0
+  // of an NVLS multicast image) instead of the staging buffer + TMA store; 0 = off
+  uint64_t plain_dst_ptr;
+  int64_t plain_dst_pitch;
   uint8_t lut1[256];
 };
 

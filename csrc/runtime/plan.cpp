@@ -479,7 +479,6 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
   if (seg.phases.size() != 2 || env_int("B200IMG_NO_SWEEP", 0) || (L.flags & B2I_LAUNCH_NO_TMA) ||
       env_int("B200IMG_NO_TMA", 0))
     return 0;
-  if (last && (L.flags & B2I_LAUNCH_DST_MCAST)) return 0;
   const PhaseDesc& g = seg.phases[0];
   const PhaseDesc& st = seg.phases[1];
   if ((g.type != PH_GRAY_REF && g.type != PH_GRAY_CV) || st.type != PH_STENCIL || st.ksize != 3 ||
@@ -515,7 +514,15 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
   const int src_rows = std::min(src.y_end, L.H) - src.y_begin;
   if (!encode_map(&src_map, src.ptr, src.pitch, (int64_t)L.W * 3, src_rows, kSweepInBytes, kSweepChunk)) return 0;
   const uint64_t dptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
-  if (!encode_map(&dst_map, dptr, dst.pitch, (int64_t)L.W * seg.cout, y1 - y0, out_row, kSweepChunk)) return 0;
+  const bool plain = last && (L.flags & B2I_LAUNCH_DST_MCAST);
+  if (plain) {  // NVLS multicast image: 8-byte stores from registers, no tensor map on that address
+    if ((dptr | (uint64_t)dst.pitch) & 7) return 0;
+    memset(&dst_map, 0, sizeof dst_map);
+    P.plain_dst_ptr = dptr;
+    P.plain_dst_pitch = dst.pitch;
+  } else if (!encode_map(&dst_map, dptr, dst.pitch, (int64_t)L.W * seg.cout, y1 - y0, out_row, kSweepChunk)) {
+    return 0;
+  }
   // segment height: a multiple of the box height, chosen so that the tasks fill the resident
   // warps evenly and the two halo rows per segment stay cheap
   P.n_strips = (L.W + kSweepStrip - 1) / kSweepStrip;
@@ -620,7 +627,6 @@ int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0
   if (seg.phases.size() != 2 || env_int("B200IMG_NO_SWEEP", 0) || env_int("B200IMG_NO_SWEEP5", 0) ||
       (L.flags & B2I_LAUNCH_NO_TMA) || env_int("B200IMG_NO_TMA", 0))
     return 0;
-  if (last && (L.flags & B2I_LAUNCH_DST_MCAST)) return 0;
   const PhaseDesc& ph = seg.phases[0];
   const PhaseDesc& pv = seg.phases[1];
   if (ph.type != PH_SEPH || pv.type != PH_SEPV || seg.cin != 3 || seg.cout != 3 || pv.expand) return 0;
@@ -651,7 +657,15 @@ int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0
   const int src_rows = std::min(src.y_end, L.H) - src.y_begin;
   if (!encode_map(&src_map, src.ptr, src.pitch, (int64_t)L.W * 3, src_rows, kS5InBytes, kS5Chunk)) return 0;
   const uint64_t dptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
-  if (!encode_map(&dst_map, dptr, dst.pitch, (int64_t)L.W * 3, y1 - y0, kS5OutBytes, kS5Chunk)) return 0;
+  const bool plain = last && (L.flags & B2I_LAUNCH_DST_MCAST);
+  if (plain) {  // NVLS multicast image: 8-byte stores from registers, no tensor map on that address
+    if ((dptr | (uint64_t)dst.pitch) & 7) return 0;
+    memset(&dst_map, 0, sizeof dst_map);
+    P.plain_dst_ptr = dptr;
+    P.plain_dst_pitch = dst.pitch;
+  } else if (!encode_map(&dst_map, dptr, dst.pitch, (int64_t)L.W * 3, y1 - y0, kS5OutBytes, kS5Chunk)) {
+    return 0;
+  }
   P.n_strips = (L.W + kS5Strip - 1) / kS5Strip;
   const int resident = sms * kS5CtasPerSm * kS5Warps;
   P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kS5Chunk, 20, 120, 4);
@@ -680,7 +694,6 @@ int try_sweep_sobel(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, i
   if (seg.phases.size() != 1 || env_int("B200IMG_NO_SWEEP", 0) || env_int("B200IMG_NO_SWEEP_SOBEL", 0) ||
       (L.flags & B2I_LAUNCH_NO_TMA) || env_int("B200IMG_NO_TMA", 0))
     return 0;
-  if (last && (L.flags & B2I_LAUNCH_DST_MCAST)) return 0;
   const PhaseDesc& ph = seg.phases[0];
   if (ph.type != PH_SOBEL || seg.cin != 3 || seg.cout != 3 || ph.expand || ph.border == B2I_BORDER_REF) return 0;
   if ((L.W & 7) || L.W < 16 || L.H < 8 || y1 - y0 < 1) return 0;
@@ -703,7 +716,15 @@ int try_sweep_sobel(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, i
   const int src_rows = std::min(src.y_end, L.H) - src.y_begin;
   if (!encode_map(&src_map, src.ptr, src.pitch, (int64_t)L.W * 3, src_rows, kSSInBytes, kSSChunk)) return 0;
   const uint64_t dptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
-  if (!encode_map(&dst_map, dptr, dst.pitch, (int64_t)L.W * 3, y1 - y0, kSSOutBytes, kSSChunk)) return 0;
+  const bool plain = last && (L.flags & B2I_LAUNCH_DST_MCAST);
+  if (plain) {  // NVLS multicast image: 8-byte stores from registers, no tensor map on that address
+    if ((dptr | (uint64_t)dst.pitch) & 7) return 0;
+    memset(&dst_map, 0, sizeof dst_map);
+    P.plain_dst_ptr = dptr;
+    P.plain_dst_pitch = dst.pitch;
+  } else if (!encode_map(&dst_map, dptr, dst.pitch, (int64_t)L.W * 3, y1 - y0, kSSOutBytes, kSSChunk)) {
+    return 0;
+  }
   P.n_strips = (L.W + kSSStrip - 1) / kSSStrip;
   const int resident = sms * kSSCtasPerSm * kSSWarps;
   P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kSSChunk, 16, 120, 2);
