@@ -54,64 +54,73 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--frames", type=int, default=256)
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--ns", default="", help="comma-separated GPU counts to measure (default 1,2,4,8 up to --gpus)")
+    ap.add_argument("--only", default="", help="comma-separated config numbers to run (default all)")
     a = ap.parse_args()
     ngpu = max(1, min(a.gpus, torch.cuda.device_count()))
     Ns = [n for n in (1, 2, 4, 8) if n <= ngpu]
+    if a.ns:
+        Ns = [int(x) for x in a.ns.split(",") if int(x) <= ngpu]
+    only = {int(x) for x in a.only.split(",")} if a.only else {1, 2, 3, 4, 5}
     res = {"gpus_available": ngpu, "hbm_gbs": HBM, "nvlink_gbs": NVL, "configs": {}}
 
     # 1. 512x512 RGB, grayscale, 2 host ranks, no GPU ------------------------------------------------
-    img = b2.synth_image(512, 512, 3, seed=1)
-    best = 1e9
-    for _ in range(20):
-        t0 = time.perf_counter()
-        out = b2.host_run("gray", img, ranks=2)
-        best = min(best, time.perf_counter() - t0)
-    res["configs"]["1_host_512_gray_np2"] = {"ms": round(best * 1e3, 4), "mpix_per_s": round(0.262144 / best, 1),
-                                             "bit_exact": bool(np.array_equal(out, b2.host_run("gray", img)))}
+    if 1 in only:
+        img = b2.synth_image(512, 512, 3, seed=1)
+        best = 1e9
+        for _ in range(20):
+            t0 = time.perf_counter()
+            out = b2.host_run("gray", img, ranks=2)
+            best = min(best, time.perf_counter() - t0)
+        res["configs"]["1_host_512_gray_np2"] = {"ms": round(best * 1e3, 4), "mpix_per_s": round(0.262144 / best, 1),
+                                                 "bit_exact": bool(np.array_equal(out, b2.host_run("gray", img)))}
 
-    # 2. 8K gray / invert / reference pipeline, root-owned scatter -> filter -> gather ---------------
     W, H = 7680, 4320
     img = b2.synth_image(W, H, 3, seed=1)
     mp = W * H / 1e6
-    c2 = {}
-    for chain, bpp in (("gray", 4), ("invert", 6), ("kernel_cu", 6)):
-        row = {"naive_1gpu_ms": round(naive_ms(chain, img), 4)}
-        for n in Ns:
-            with Runtime(gpus=n) as rt:
-                rt.run(img, chain, mode="root", iters=3)
-                rt.run(img, chain, mode="root", iters=20)
-                ms_equal = rt.last_ms
-                rt.run(img, chain, mode="root", iters=20, root_share="auto")   # link-aware bands
-                ms, share = rt.last_ms, getattr(rt, "root_share", None)
-            # roofline of the band plan actually used: the root's share at HBM speed, the rest through the
-            # root's NVLink port (input one way, output the other way, concurrently)
-            f_root = 1.0 if n == 1 else (share if share else 1.0 / n)
-            link_ms = (1 - f_root) * W * H * max(3, bpp - 3) / (NVL * 1e6)
-            roof_ms = max(f_root * W * H * bpp / (HBM * 1e6), link_ms)
-            row[f"n{n}"] = {"ms": round(ms, 4), "mpix_per_s": round(mp / ms * 1e3, 1),
-                            "equal_bands_ms": round(ms_equal, 4), "root_share": None if share is None else round(share, 3),
-                            "roofline_ms": round(roof_ms, 4), "of_roofline": round(roof_ms / ms, 3)}
-        c2[chain] = row
-    res["configs"]["2_8k_root_scatter_filter_gather"] = c2
+    # 2. 8K gray / invert / reference pipeline, root-owned scatter -> filter -> gather ---------------
+    if 2 in only:
+        c2 = {}
+        for chain, bpp in (("gray", 4), ("invert", 6), ("kernel_cu", 6)):
+            row = {"naive_1gpu_ms": round(naive_ms(chain, img), 4)}
+            for n in Ns:
+                with Runtime(gpus=n) as rt:
+                    rt.run(img, chain, mode="root", iters=3)
+                    rt.run(img, chain, mode="root", iters=20)
+                    ms_equal = rt.last_ms
+                    rt.run(img, chain, mode="root", iters=20, root_share="auto")   # link-aware bands
+                    ms, share = rt.last_ms, getattr(rt, "root_share", None)
+                # roofline of the band plan actually used: the root's share at HBM speed, the rest through the
+                # root's NVLink port (input one way, output the other way, concurrently)
+                f_root = 1.0 if n == 1 else (share if share else 1.0 / n)
+                link_ms = (1 - f_root) * W * H * max(3, bpp - 3) / (NVL * 1e6)
+                roof_ms = max(f_root * W * H * bpp / (HBM * 1e6), link_ms)
+                row[f"n{n}"] = {"ms": round(ms, 4), "mpix_per_s": round(mp / ms * 1e3, 1),
+                                "equal_bands_ms": round(ms_equal, 4), "root_share": None if share is None else round(share, 3),
+                                "roofline_ms": round(roof_ms, 4), "of_roofline": round(roof_ms / ms, 3)}
+            c2[chain] = row
+        res["configs"]["2_8k_root_scatter_filter_gather"] = c2
 
     # 3. 8K RGB 5x5 Gaussian, bands resident, halo push fused into the kernel ---------------------------
-    c3 = {"naive_1gpu_ms": round(naive_ms("gauss5", img), 4)}
-    for n in Ns:
-        with Runtime(gpus=n) as rt:
-            rt.run(img, "gauss5", mode="resident", passes=4)
-            rt.run(img, "gauss5", mode="resident", passes=16)
-            ms_e = rt.last_ms
-            rt.run(img, "gauss5", mode="resident", passes=16, sync="flags")
-            ms_f = rt.last_ms
-        roof_ms = W * H * 6 / n / (HBM * 1e6)
-        c3[f"n{n}"] = {"ms_per_pass_events": round(ms_e, 4), "ms_per_pass_flags": round(ms_f, 4),
-                       "mpix_per_s": round(mp / min(ms_e, ms_f) * 1e3, 1), "roofline_ms": round(roof_ms, 4),
-                       "of_roofline": round(roof_ms / min(ms_e, ms_f), 3), "halo_bytes_per_pass": 2 * 2 * W * 3}
-    res["configs"]["3_8k_gauss5_resident_halo"] = c3
+    if 3 in only:
+        c3 = {"naive_1gpu_ms": round(naive_ms("gauss5", img), 4)}
+        for n in Ns:
+            with Runtime(gpus=n) as rt:
+                rt.run(img, "gauss5", mode="resident", passes=4)
+                rt.run(img, "gauss5", mode="resident", passes=16)
+                ms_e = rt.last_ms
+                rt.run(img, "gauss5", mode="resident", passes=16, sync="flags")
+                ms_f = rt.last_ms
+            roof_ms = W * H * 6 / n / (HBM * 1e6)
+            c3[f"n{n}"] = {"ms_per_pass_events": round(ms_e, 4), "ms_per_pass_flags": round(ms_f, 4),
+                           "mpix_per_s": round(mp / min(ms_e, ms_f) * 1e3, 1), "roofline_ms": round(roof_ms, 4),
+                           "of_roofline": round(roof_ms / min(ms_e, ms_f), 3), "halo_bytes_per_pass": 2 * 2 * W * 3}
+        res["configs"]["3_8k_gauss5_resident_halo"] = c3
+
     del img
 
     # 4. 16K x 16K RGB blur -> Sobel, resident ----------------------------------------------------------
-    if not a.quick:
+    if 4 in only and not a.quick:
         W4 = H4 = 16384
         img4 = b2.synth_image(W4, H4, 3, seed=2)
         mp4 = W4 * H4 / 1e6
@@ -128,40 +137,41 @@ def main():
         del img4
 
     # 5. batch of 4K frames from pinned host memory through grayscale + blur ---------------------------
-    Wf, Hf, F = 3840, 2160, a.frames if not a.quick else 32
-    base = torch.from_numpy(b2.synth_image(Wf, Hf, 3, seed=3))
-    NPOOL = 16  # distinct pinned frames cycled through (F x 24.9 MB would be 6.4 GB of pinned memory)
-    fin = [base.clone().pin_memory() for _ in range(NPOOL)]
-    fout = [torch.empty((Hf, Wf, 1), dtype=torch.uint8).pin_memory() for _ in range(NPOOL)]
-    c5 = {}
-    for n in Ns:
-        bs = BatchStreamer("gray,gauss5", gpus=n)
-        ins = [fin[i % NPOOL] for i in range(F)]
-        outs = [fout[i % NPOOL] for i in range(F)]
-        bs.run(ins[:2 * n], outs[:2 * n])
-        for g in range(n):
-            torch.cuda.synchronize(g)
+    if 5 in only:
+        Wf, Hf, F = 3840, 2160, a.frames if not a.quick else 32
+        base = torch.from_numpy(b2.synth_image(Wf, Hf, 3, seed=3))
+        NPOOL = 16  # distinct pinned frames cycled through (F x 24.9 MB would be 6.4 GB of pinned memory)
+        fin = [base.clone().pin_memory() for _ in range(NPOOL)]
+        fout = [torch.empty((Hf, Wf, 1), dtype=torch.uint8).pin_memory() for _ in range(NPOOL)]
+        c5 = {}
+        for n in Ns:
+            bs = BatchStreamer("gray,gauss5", gpus=n)
+            ins = [fin[i % NPOOL] for i in range(F)]
+            outs = [fout[i % NPOOL] for i in range(F)]
+            bs.run(ins[:2 * n], outs[:2 * n])
+            for g in range(n):
+                torch.cuda.synchronize(g)
+            t0 = time.perf_counter()
+            bs.run(ins, outs)
+            for g in range(n):
+                torch.cuda.synchronize(g)
+            dt = time.perf_counter() - t0
+            c5[f"n{n}"] = {"frames": F, "ms_per_frame": round(dt / F * 1e3, 4), "fps": round(F / dt, 1),
+                           "mpix_per_s": round(F * Wf * Hf / 1e6 / dt, 1),
+                           "h2d_gbs": round(F * Wf * Hf * 3 / dt / 1e9, 1), "d2h_gbs": round(F * Wf * Hf / dt / 1e9, 1)}
+        want = b2.host_run("gray,gauss5", base.numpy(), rows=(100, 132))
+        c5["bit_exact_rows_100_132"] = bool(np.array_equal(fout[0].numpy()[100:132], want))
+        # the reference's pattern: pageable synchronous copies, one frame at a time (kernel.cu:163,202)
+        p = Plan("gray,gauss5", 3)
+        pag = base.clone()
         t0 = time.perf_counter()
-        bs.run(ins, outs)
-        for g in range(n):
-            torch.cuda.synchronize(g)
-        dt = time.perf_counter() - t0
-        c5[f"n{n}"] = {"frames": F, "ms_per_frame": round(dt / F * 1e3, 4), "fps": round(F / dt, 1),
-                       "mpix_per_s": round(F * Wf * Hf / 1e6 / dt, 1),
-                       "h2d_gbs": round(F * Wf * Hf * 3 / dt / 1e9, 1), "d2h_gbs": round(F * Wf * Hf / dt / 1e9, 1)}
-    want = b2.host_run("gray,gauss5", base.numpy(), rows=(100, 132))
-    c5["bit_exact_rows_100_132"] = bool(np.array_equal(fout[0].numpy()[100:132], want))
-    # the reference's pattern: pageable synchronous copies, one frame at a time (kernel.cu:163,202)
-    p = Plan("gray,gauss5", 3)
-    pag = base.clone()
-    t0 = time.perf_counter()
-    for _ in range(16):
-        d = pag.cuda()
-        o = p.run(d)
-        _ = o.cpu()
-    dt = (time.perf_counter() - t0) / 16
-    c5["pageable_sync_1gpu"] = {"ms_per_frame": round(dt * 1e3, 3), "mpix_per_s": round(Wf * Hf / 1e6 / dt, 1)}
-    res["configs"]["5_batch_4k_gray_blur_stream"] = c5
+        for _ in range(16):
+            d = pag.cuda()
+            o = p.run(d)
+            _ = o.cpu()
+        dt = (time.perf_counter() - t0) / 16
+        c5["pageable_sync_1gpu"] = {"ms_per_frame": round(dt * 1e3, 3), "mpix_per_s": round(Wf * Hf / 1e6 / dt, 1)}
+        res["configs"]["5_batch_4k_gray_blur_stream"] = c5
 
     txt = json.dumps(res, indent=1)
     print(txt)

@@ -119,6 +119,24 @@ __device__ __forceinline__ bool wait_flag_ge(const uint32_t* p, uint32_t want,
   }
 }
 
+// End of a sweep kernel (lane 0 of every warp that had work, after its stores have completed): the
+// last warp to arrive waits for the other GPUs' done flags (the root's side) and / or publishes this
+// GPU's done flag (everyone else's side) -- MPI_Gather's completion (kernel.cu:223) without a
+// separate kernel. counter: a zeroed u32 that is left zeroed.
+__device__ __forceinline__ void sweep_finish(uint32_t* counter, uint32_t n_warps, uint64_t done_flag, uint32_t epoch,
+                                             uint64_t wait_flags, uint32_t wait_mask, uint32_t* status,
+                                             unsigned long long timeout_ns) {
+  asm volatile("fence.proxy.async;" ::: "memory");  // TMA stores (async proxy) before the flag (generic proxy)
+  __threadfence_system();
+  if (atomicAdd(counter, 1u) + 1 != n_warps) return;
+  atomicExch(counter, 0u);
+  for (uint32_t m = wait_mask; m; m &= m - 1) {
+    const int r = __ffs(m) - 1;
+    if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(wait_flags) + r, epoch, timeout_ns)) atomicExch(status, 3u);
+  }
+  if (done_flag) st_release_sys(reinterpret_cast<uint32_t*>(done_flag), epoch);
+}
+
 // ---- streaming vector loads/stores (local HBM or NVLink peer memory) --------------------------
 __device__ __forceinline__ uint4 ldg_stream_v4(const void* p) {
   uint4 r;

@@ -24,6 +24,9 @@ struct SweepParams {
   int32_t border, shift, bias, expand;
   int32_t warp_smem;          // bytes of dynamic shared memory per warp
   int32_t in_stage_bytes, out_buf_bytes;  // 128-byte aligned sizes of one input stage / one staging buffer
+  // completion flags (multi-GPU ROOT mode): see sweep_finish in device_utils.cuh
+  uint64_t done_flag, wait_done_flags, counters, status, timeout_ns;
+  uint32_t wait_done_mask, signal_epoch;
   // replicated output: result rows leave by 8-byte stores from registers to this address (row y0
   // of an NVLS multicast image) instead of the staging buffer + TMA store; 0 = off
   uint64_t plain_dst_ptr;

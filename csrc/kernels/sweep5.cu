@@ -315,7 +315,15 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
       }
     }
   }
-  if (lane == 0) tma_store_wait_all();
+  if (P.done_flag | P.wait_done_mask) __threadfence_system();  // every lane's plain stores before the flag
+  __syncwarp();
+  if (lane == 0) {
+    tma_store_wait_all();
+    if ((P.done_flag | P.wait_done_mask) && blockIdx.x * kS5Warps + warp < P.n_tasks)
+      sweep_finish(reinterpret_cast<uint32_t*>(P.counters) + 2, (uint32_t)min(total_warps, P.n_tasks), P.done_flag,
+                   P.signal_epoch, P.wait_done_flags, P.wait_done_mask, reinterpret_cast<uint32_t*>(P.status),
+                   P.timeout_ns);
+  }
 }
 
 }  // namespace

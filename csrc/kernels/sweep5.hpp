@@ -30,6 +30,9 @@ struct Sweep5Params {
   uint64_t push_up_ptr, push_dn_ptr;       // where row y0 / row y1 - push_rows lands at the neighbour
   uint64_t wait_up_flag, wait_dn_flag, signal_up_flag, signal_dn_flag;
   uint64_t counters, status, timeout_ns;
+  // completion flags (multi-GPU ROOT mode): see sweep_finish in device_utils.cuh
+  uint64_t done_flag, wait_done_flags;
+  uint32_t wait_done_mask, reserved0;
   // replicated output: result rows leave by 8-byte stores from registers to this address (row y0
   // of an NVLS multicast image) instead of the staging buffer + TMA store; 0 = off
   uint64_t plain_dst_ptr;

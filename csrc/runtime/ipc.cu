@@ -7,6 +7,8 @@
 // ever does. MPI_Barrier (kernel.cu:127,133) becomes device-side epoch flags.
 #include <cuda_runtime.h>
 
+#include <algorithm>
+
 #include <cstring>
 
 #include "../core/error.hpp"
@@ -132,14 +134,34 @@ extern "C" int b2i_cuda_run_steps(b2i_plan_t* plan, const b2i_launch_t* launch, 
                                   uint64_t signal_flag) {
   B2I_CHECK_ARG(plan && launch && steps >= 0, "bad arguments");
   b2i_launch_t L = *launch;
+  // The flags ride in the launch: the sweep kernels publish / wait in their last warp, any other
+  // kernel is followed by one-thread flag kernels (b2i_cuda_run). The fused wait wants the flags
+  // as one u32 array; anything else keeps the separate wait kernel.
+  const bool empty = L.y0 == L.y1;  // no rows: no kernel to carry the flags
+  L.done_flag = empty ? 0 : signal_flag;
+  bool fused_wait = false;
+  if (n_wait > 0 && !empty) {
+    uint64_t base = wait_flags[0];
+    for (int k = 1; k < n_wait; ++k) base = std::min(base, wait_flags[k]);
+    uint32_t mask = 0;
+    bool ok = true;
+    for (int k = 0; k < n_wait; ++k) {
+      const uint64_t off = wait_flags[k] - base;
+      if ((off & 3) || off / 4 >= B2I_MAX_GPUS) ok = false;
+      else mask |= 1u << (off / 4);
+    }
+    if (ok) {
+      L.wait_done_flags = base;
+      L.wait_done_mask = mask;
+      fused_wait = true;
+    }
+  }
   for (int i = 0; i < steps; ++i) {
     const uint32_t epoch = epoch_base + (uint32_t)i + 1;
     L.signal_epoch = epoch;
     B2I_TRY(b2i_cuda_run(plan, &L));
-    // "my rows of image i are in the root image": published by a one-thread kernel that runs
-    // after the filter kernel in stream order (all of its TMA stores have completed by then)
-    if (signal_flag) B2I_TRY(b2i_cuda_set_flags(&signal_flag, 1, epoch, L.stream));
-    if (n_wait > 0) {
+    if (empty && signal_flag) B2I_TRY(b2i_cuda_set_flags(&signal_flag, 1, epoch, L.stream));
+    if (n_wait > 0 && !fused_wait) {
       B2I_CHECK_ARG(L.status, "waiting needs the status word");
       B2I_TRY(b2i_cuda_wait_flags(wait_flags, n_wait, epoch, L.status, L.timeout_ns, L.stream));
     }

@@ -471,6 +471,21 @@ int env_int(const char* name, int dflt) {
   return v && *v ? atoi(v) : dflt;
 }
 
+// Completion flags of ROOT mode, fused into the end of a sweep kernel (device_utils.cuh:
+// sweep_finish). Tells b2i_cuda_run that no separate wait kernel is needed.
+thread_local bool g_wait_done_fused = false;
+template <class Params>
+void sweep_finish_fill(Params& P, const b2i_launch_t& L) {
+  P.done_flag = L.done_flag;
+  P.wait_done_flags = L.wait_done_flags;
+  P.wait_done_mask = L.wait_done_flags ? L.wait_done_mask : 0;
+  P.signal_epoch = L.signal_epoch;
+  P.counters = L.counters;
+  P.status = L.status;
+  P.timeout_ns = L.timeout_ns ? L.timeout_ns : 2000000000ull;
+  g_wait_done_fused = true;
+}
+
 // The warp-sweep kernel (kernels/sweep3.cu) takes segments of the reference's own shape:
 // gray (+LUT) -> one 3x3 stencil on the gray plane (+LUT, +expand). Returns 1 if it launched,
 // 0 if the segment or the buffers do not qualify (the tile-chain kernel then runs it).
@@ -485,8 +500,10 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
       st.cin != 1 || seg.cin != 3)
     return 0;
   if ((L.push_rows && (L.push_up.ptr || L.push_dn.ptr)) || L.wait_up_flag || L.wait_dn_flag ||
-      L.signal_up_flag || L.signal_dn_flag || L.done_flag)
+      L.signal_up_flag || L.signal_dn_flag)
     return 0;
+  const bool finish = last && (L.done_flag || L.wait_done_mask);
+  if (finish && !(L.counters && L.status)) return 0;
   if ((L.W & 7) || L.W < 16 || y1 - y0 < 1) return 0;
   SweepParams P;
   memset(&P, 0, sizeof P);
@@ -545,6 +562,7 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
   plan->info.last_blocks_per_sm = kSweepCtasPerSm;
   plan->info.last_tma_load = plan->info.last_tma_store = 1;
   plan->info.last_launches++;
+  if (finish) sweep_finish_fill(P, L);
   cudaError_t e = launch_sweep3(P, src_map, dst_map, grid, (cudaStream_t)L.stream);
   if (e != cudaSuccess) {
     b2i::fail(B2I_ERR_CUDA, __FILE__, __LINE__, "sweep3 launch: %s", cudaGetErrorString(e));
@@ -558,7 +576,6 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
 // segment's result rows. Returns false if the launch asks for something the sweeps do not do (the
 // tile kernel then runs it, or reports the error).
 bool sweep_hooks_ok(const b2i_launch_t& L, int y0, int y1, bool first, bool last, bool* pushes, bool* flags) {
-  if (L.done_flag) return false;
   *pushes = last && L.push_rows > 0 && (L.push_up.ptr || L.push_dn.ptr);
   *flags = (first && (L.wait_up_flag || L.wait_dn_flag)) || (last && (L.signal_up_flag || L.signal_dn_flag));
   if (*pushes) {
@@ -569,9 +586,10 @@ bool sweep_hooks_ok(const b2i_launch_t& L, int y0, int y1, bool first, bool last
     if (L.push_up.ptr && (L.push_up.y_begin > y0 || L.push_up.y_end < y0 + L.push_rows)) return false;
     if (L.push_dn.ptr && (L.push_dn.y_begin > y1 - L.push_rows || L.push_dn.y_end < y1)) return false;
   }
-  if (*flags && !(L.counters && L.status)) return false;
+  if ((*flags || (last && (L.done_flag || L.wait_done_mask))) && !(L.counters && L.status)) return false;
   return true;
 }
+
 
 template <class Params>
 void sweep_hooks_fill(Params& P, const b2i_launch_t& L, int y0, int y1, bool first, bool last, bool pushes) {
@@ -679,6 +697,7 @@ int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0
   plan->info.last_blocks_per_sm = kS5CtasPerSm;
   plan->info.last_tma_load = plan->info.last_tma_store = 1;
   plan->info.last_launches++;
+  if (last && (L.done_flag || L.wait_done_mask)) sweep_finish_fill(P, L);
   cudaError_t e = launch_sweep5(P, src_map, dst_map, grid, (cudaStream_t)L.stream);
   if (e != cudaSuccess) {
     b2i::fail(B2I_ERR_CUDA, __FILE__, __LINE__, "sweep5 launch: %s", cudaGetErrorString(e));
@@ -738,6 +757,7 @@ int try_sweep_sobel(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, i
   plan->info.last_blocks_per_sm = kSSCtasPerSm;
   plan->info.last_tma_load = plan->info.last_tma_store = 1;
   plan->info.last_launches++;
+  if (last && (L.done_flag || L.wait_done_mask)) sweep_finish_fill(P, L);
   cudaError_t e = launch_sweep_sobel(P, src_map, dst_map, grid, (cudaStream_t)L.stream);
   if (e != cudaSuccess) {
     b2i::fail(B2I_ERR_CUDA, __FILE__, __LINE__, "sweep_sobel launch: %s", cudaGetErrorString(e));
@@ -890,7 +910,7 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
   if (last) {
     P.signal_up_flag = L.signal_up_flag;
     P.signal_dn_flag = L.signal_dn_flag;
-    P.done_flag = L.done_flag;
+    P.done_flag = 0;  // completion flags: the sweep kernels fuse them, b2i_cuda_run follows up otherwise
     P.signal_epoch = L.signal_epoch;
     if (L.push_rows > 0 && (L.push_up.ptr || L.push_dn.ptr)) {
       B2I_CHECK_ARG(L.push_rows <= y1 - y0 && L.push_rows <= kGhostRows,
@@ -998,9 +1018,9 @@ int launch_pointwise_segment(b2i_plan* plan, const Segment& seg, const b2i_launc
   P.dst_ptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
   P.vec_ok = !((P.src_ptr | P.dst_ptr | (uint64_t)P.src_pitch | (uint64_t)P.dst_pitch) & 15) &&
              !env_int("B200IMG_NO_VEC", 0);
-  if (last && L.done_flag) {
+  if (false && last && L.done_flag) {
     B2I_CHECK_ARG(L.counters, "done_flag needs the counters scratch words");
-    P.done_flag = L.done_flag;
+    P.done_flag = 0;  // completion flags: the sweep kernels fuse them, b2i_cuda_run follows up otherwise
     P.counters = L.counters;
     P.signal_epoch = L.signal_epoch;
   }
@@ -1095,7 +1115,7 @@ extern "C" int b2i_cuda_run(b2i_plan_t* plan, const b2i_launch_t* Lp) {
   const bool use_split = !plan->segs_split.empty() && !(L.flags & (B2I_LAUNCH_NO_TMA | B2I_LAUNCH_NAIVE)) &&
                          !(L.W & 7) && L.W >= 16 && L.H >= 8 && tma_ok(L.src) && tma_ok(L.dst) &&
                          tma_ok(L.tmp[0]) && (plan->segs_split.size() < 3 || tma_ok(L.tmp[1])) &&
-                         L.tmp[0].pitch >= (int64_t)L.W * 3 && !L.done_flag && tensor_map_encoder() &&
+                         L.tmp[0].pitch >= (int64_t)L.W * 3 && tensor_map_encoder() &&
                          !env_int("B200IMG_NO_SWEEP", 0) && !env_int("B200IMG_NO_TMA", 0) &&
                          !env_int("B200IMG_NO_SPLIT", 0);
   const std::vector<Segment>& segs = use_split ? plan->segs_split : plan->segs;
@@ -1132,9 +1152,20 @@ extern "C" int b2i_cuda_run(b2i_plan_t* plan, const b2i_launch_t* Lp) {
       B2I_CHECK_ARG(out.ptr, "plan has %d segments: tmp[%d] is needed", n, s & 1);
       B2I_CHECK_ARG(out.pitch >= (int64_t)L.W * seg.cout, "tmp pitch too small");
     }
+    if (last) g_wait_done_fused = false;
     if (seg.pointwise) B2I_TRY(launch_pointwise_segment(plan, seg, L, ya, yb, cur, out, last));
     else B2I_TRY(launch_tile_segment(plan, seg, L, ya, yb, cur, out, s == 0, last));
     cur = out;
+    if (last && L.done_flag && !g_wait_done_fused)  // kernels without the fused flags: one-thread kernels follow
+      B2I_TRY(b2i_cuda_set_flags(&L.done_flag, 1, L.signal_epoch, L.stream));
+    if (last && L.wait_done_mask && L.wait_done_flags && !g_wait_done_fused) {
+      uint64_t fl[B2I_MAX_GPUS];
+      int nf = 0;
+      for (int r = 0; r < B2I_MAX_GPUS; ++r)
+        if (L.wait_done_mask >> r & 1) fl[nf++] = L.wait_done_flags + 4ull * r;
+      B2I_CHECK_ARG(L.status, "waiting needs the status word");
+      B2I_TRY(b2i_cuda_wait_flags(fl, nf, L.signal_epoch, L.status, L.timeout_ns, L.stream));
+    }
     if (!last) {  // later segments may read exactly what this one produced
       cur.ptr = out.ptr + (uint64_t)((int64_t)(ya - out.y_begin) * out.pitch);
       cur.y_begin = ya;

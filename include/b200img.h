@@ -189,6 +189,12 @@ typedef struct b2i_launch {
   void* stream;                            /* cudaStream_t */
   int32_t tile_h;                          /* 0 = choose */
   int32_t flags;                           /* B2I_LAUNCH_* */
+  /* The root's side of done_flag: u32 flags [0..B2I_MAX_GPUS) in local memory, one per GPU; the
+   * launch returns (in stream order) only after every flag selected by the mask has reached
+   * signal_epoch. The sweep kernels do this wait in their last warp, other kernels are followed
+   * by a one-thread wait kernel. 0 = off. */
+  uint64_t wait_done_flags;
+  uint32_t wait_done_mask, reserved0;
 } b2i_launch_t;
 
 typedef struct b2i_plan_info {

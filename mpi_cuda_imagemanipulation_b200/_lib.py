@@ -133,6 +133,7 @@ class Launch(C.Structure):
         ("done_flag", C.c_uint64), ("counters", C.c_uint64), ("status", C.c_uint64),
         ("timeout_ns", C.c_uint64), ("stream", C.c_void_p),
         ("tile_h", C.c_int32), ("flags", C.c_int32),
+        ("wait_done_flags", C.c_uint64), ("wait_done_mask", C.c_uint32), ("reserved0", C.c_uint32),
     ]
 
 

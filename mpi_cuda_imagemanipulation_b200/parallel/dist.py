@@ -240,9 +240,22 @@ class DistRuntime:
         r_root = t[2].item() / max(tmax[0].item(), 1e-6)
         r_rem = t[3].item() / max(tmax[1].item(), 1e-6)  # remotes run concurrently on one shared link
         share = r_root / (r_root + r_rem)
-        self.set_root_share(share)
+        # The model ignores what the two sides do to each other: peer traffic into the root's HBM
+        # slows the root's own kernel (measured at N = 2: 25 %), and every remote band costs a flag
+        # round trip. So the model's share and a few larger ones are timed as whole steps, and the
+        # fastest wins -- up to 1.0, where the root keeps everything because the link cannot pay
+        # for itself. All ranks see the same all-reduced times, hence pick the same share.
+        best, best_ms = share, None
+        for cand in sorted({min(1.0, round(share + d, 3)) for d in (0.0, 0.04, 0.08, 0.12)} | {1.0}):
+            self.set_root_share(cand)
+            self.run_root(plan, 2)
+            self.barrier()
+            ms_c = min(_timed(lambda: self.run_root(plan, steps)) / steps for _ in range(2))
+            if best_ms is None or ms_c < best_ms * 0.98:   # a larger share must win clearly
+                best, best_ms = cand, ms_c
+        self.set_root_share(best)
         self.barrier()
-        return share
+        return best
 
     # ---- RESIDENT mode: bands (+ghost rows) stay on their GPUs, kernels push halos ---------------------
     def setup_resident(self, W: int, H: int, Cn: int):
@@ -452,8 +465,10 @@ def bench_distributed(args, rank: int, world: int, local: int) -> Optional[dict]
                        "image": f"{W}x{H} RGB", "global_batch": 1, "seq_len": W * H, "parallelism": f"bands{world}",
                        "mode": "root-owned input and output on GPU 0; scatter and gather fused into the filter "
                                "kernel over NVLink peer memory (IPC), done flags acquired on the root each step",
-                       "bands": f"root GPU takes {share:.3f} of the rows (measured: its local rate vs the other ranks' "
-                                f"combined rate through the root's NVLink port), the other {world - 1} split the rest",
+                       "bands": f"root GPU takes {share:.3f} of the rows, the other {world - 1} split the rest: the share is "
+                                f"the fastest of the link model's (root's local rate vs the others' combined rate through "
+                                f"the root's one NVLink port) and a few larger ones, timed as whole steps; 1.000 means the "
+                                f"link cannot pay for itself on this filter and the root keeps the image",
                        "equal_bands_ms_per_step": round(ms_equal, 6),
                        "l2": "input 99.5 MB + output 99.5 MB per step; remote ranks bypass the root's L2 for peer traffic",
                        "timed_as": f"{K} steps per replay from C, CUDA events per rank, max over ranks, median of {args.repeats}"},
