@@ -90,6 +90,13 @@ def main():
                     ms_equal = rt.last_ms
                     rt.run(img, chain, mode="root", iters=20, root_share="auto")   # link-aware bands
                     ms, share = rt.last_ms, getattr(rt, "root_share", None)
+                    rep_ms = None
+                    if n > 1 and chain == "kernel_cu":   # same step, result on every GPU through one NVLS multicast store
+                        try:
+                            rt.run(img, chain, mode="root", iters=20, replicate=True)
+                            rep_ms = (rt.last_ms, bool(rt.nvls))
+                        except Exception as e:
+                            rep_ms = (None, str(e)[:80])
                 # roofline of the band plan actually used: the root's share at HBM speed, the rest through the
                 # root's NVLink port (input one way, output the other way, concurrently)
                 f_root = 1.0 if n == 1 else (share if share else 1.0 / n)
@@ -98,6 +105,8 @@ def main():
                 row[f"n{n}"] = {"ms": round(ms, 4), "mpix_per_s": round(mp / ms * 1e3, 1),
                                 "equal_bands_ms": round(ms_equal, 4), "root_share": None if share is None else round(share, 3),
                                 "roofline_ms": round(roof_ms, 4), "of_roofline": round(roof_ms / ms, 3)}
+                if rep_ms:
+                    row[f"n{n}"]["replicated_output_equal_bands"] = {"ms": rep_ms[0] and round(rep_ms[0], 4), "nvls_multicast": rep_ms[1]}
             c2[chain] = row
         res["configs"]["2_8k_root_scatter_filter_gather"] = c2
 

@@ -290,7 +290,7 @@ extern "C" int b2i_ctx_load_root(b2i_ctx* c, const uint8_t* src, int W, int H, i
 }
 
 extern "C" int b2i_ctx_set_root_share(b2i_ctx* c, double share) {
-  B2I_CHECK_ARG(c && share >= 0 && share < 1, "share must be in [0,1)");
+  B2I_CHECK_ARG(c && share >= 0 && share <= 1, "share must be in [0,1]");
   c->root_share = share;
   return B2I_OK;
 }
