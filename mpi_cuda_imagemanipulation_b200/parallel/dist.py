@@ -362,6 +362,11 @@ def bench_distributed(args, rank: int, world: int, local: int) -> Optional[dict]
         want = b2.host_run(chain, img, rows=(y, y + 16))
         assert (got[y:y + 16] == want).all(), "bench output mismatch (band boundary)"
     info = plan.info()
+    # kernels launched per timed step, summed over ranks: a rank without rows launches nothing, and
+    # the completion flags ride in the sweep kernel (no separate flag kernels)
+    nl = torch.tensor([float(info["launches"]) if rt.y1 > rt.y0 else 0.0], device=rt.device)
+    dist.all_reduce(nl, op=dist.ReduceOp.SUM)
+    launches_per_step = int(nl.item())
     with ClockSampler(local) as clk:
         reps = [_timed(lambda: rt.run_root(plan, K)) / K for _ in range(args.repeats)]
         # keep the GPUs busy ~0.5 s so nvidia-smi samples clocks under this load. The repeat count
@@ -478,7 +483,7 @@ def bench_distributed(args, rank: int, world: int, local: int) -> Optional[dict]
                     "how": "root-owned pinned host image in POSIX shared memory; every rank copies its band (+halo) "
                            "over its own PCIe link, filters it and copies its rows back; 3 frames in flight per "
                            "rank on copy/compute/copy streams; CUDA events, max over ranks"},
-            "gpu_launches": K * info["launches"] * world + K * (1 if world > 1 else 0),
+            "gpu_launches": K * launches_per_step,
             "kernel": {"tile_h": info["tile_h"], "grid": info["grid"], "tma_load": info["tma_load"],
                        "tma_store": info["tma_store"]},
             "extras": extras, "impl": "ours",
