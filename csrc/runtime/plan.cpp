@@ -486,6 +486,8 @@ void sweep_finish_fill(Params& P, const b2i_launch_t& L) {
   g_wait_done_fused = true;
 }
 
+int sweep_seg_rows(int n_strips, int rows, int resident, int chunk, int lo, int hi, int halo_rows);
+
 // The warp-sweep kernel (kernels/sweep3.cu) takes segments of the reference's own shape:
 // gray (+LUT) -> one 3x3 stencil on the gray plane (+LUT, +expand). Returns 1 if it launched,
 // 0 if the segment or the buffers do not qualify (the tile-chain kernel then runs it).
@@ -544,16 +546,7 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
   // warps evenly and the two halo rows per segment stay cheap
   P.n_strips = (L.W + kSweepStrip - 1) / kSweepStrip;
   const int resident = sms * kSweepCtasPerSm * kSweepWarps;
-  double best = -1;
-  for (int sr = 15; sr <= 96; sr += kSweepChunk) {
-    const long long tasks = (long long)P.n_strips * ((y1 - y0 + sr - 1) / sr);
-    const long long waves = (tasks + resident - 1) / resident;
-    const double eff = (double)tasks / (double)(waves * resident) * sr / (sr + 2.0);
-    if (eff > best + 1e-9) {
-      best = eff;
-      P.seg_rows = sr;
-    }
-  }
+  P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kSweepChunk, 6, 96, 2);
   P.n_tasks = P.n_strips * ((y1 - y0 + P.seg_rows - 1) / P.seg_rows);
   const int grid = std::max(1, std::min((P.n_tasks + kSweepWarps - 1) / kSweepWarps, sms * kSweepCtasPerSm));
   plan->info.last_tile_h = -P.seg_rows;  // negative: rows per sweep segment
@@ -620,15 +613,18 @@ void sweep_hooks_fill(Params& P, const b2i_launch_t& L, int y0, int y1, bool fir
   P.timeout_ns = L.timeout_ns ? L.timeout_ns : 2000000000ull;
 }
 
-// Rows per sweep segment: a multiple of the box height, chosen so that the tasks fill the resident
-// warps evenly and the halo rows read twice per segment stay cheap.
+// Rows per sweep segment: a multiple of the box height that maximises rows per warp-time. A task
+// costs its rows, the halo rows it reads again, and a fixed part (first TMA round trip, pipeline
+// fill, store drain: about six rows' worth, measured on small bands with scripts/resident_probe.py).
+// Big images end up with one or two waves of tall segments; small bands (a resident pass at N = 8
+// is 540 rows per GPU) with short ones, where the run time is one task's latency.
 int sweep_seg_rows(int n_strips, int rows, int resident, int chunk, int lo, int hi, int halo_rows) {
   double best = -1;
   int pick = lo;
   for (int sr = lo; sr <= hi; sr += chunk) {
     const long long tasks = (long long)n_strips * ((rows + sr - 1) / sr);
     const long long waves = (tasks + resident - 1) / resident;
-    const double eff = (double)tasks / (double)(waves * resident) * sr / (sr + (double)halo_rows);
+    const double eff = (double)tasks / (double)(waves * resident) * sr / (sr + (double)halo_rows + 6.0);
     if (eff > best + 1e-9) {
       best = eff;
       pick = sr;
@@ -686,7 +682,7 @@ int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0
   }
   P.n_strips = (L.W + kS5Strip - 1) / kS5Strip;
   const int resident = sms * kS5CtasPerSm * kS5Warps;
-  P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kS5Chunk, 20, 120, 4);
+  P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kS5Chunk, 5, 120, 4);
   P.n_segs = (y1 - y0 + P.seg_rows - 1) / P.seg_rows;
   P.n_tasks = P.n_strips * P.n_segs;
   if (pushes || flags) sweep_hooks_fill(P, L, y0, y1, first, last, pushes);
@@ -746,7 +742,7 @@ int try_sweep_sobel(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, i
   }
   P.n_strips = (L.W + kSSStrip - 1) / kSSStrip;
   const int resident = sms * kSSCtasPerSm * kSSWarps;
-  P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kSSChunk, 16, 120, 2);
+  P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kSSChunk, 4, 120, 2);
   P.n_segs = (y1 - y0 + P.seg_rows - 1) / P.seg_rows;
   P.n_tasks = P.n_strips * P.n_segs;
   if (pushes || flags) sweep_hooks_fill(P, L, y0, y1, first, last, pushes);
