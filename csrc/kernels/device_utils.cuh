@@ -86,12 +86,24 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
 }
 
 // ---- NVLS multicast stores ------------------------------------------------------------------------
-// 8 bytes to a multicast address (b2i_mcast_ptr): the NVSwitch replicates the store into every
-// bound GPU's copy. On an ordinary address it is an ordinary store (same SASS: STG.E.64).
-__device__ __forceinline__ void st_mc_v2(uint64_t addr, uint32_t a, uint32_t b) {
-  asm volatile("multimem.st.global.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(__uint_as_float(a)),
-               "f"(__uint_as_float(b))
+// Stores to a multicast address (b2i_mcast_ptr): the NVSwitch replicates them into every bound
+// GPU's copy. On an ordinary address they are ordinary stores (same SASS: STG.E.128).
+
+__device__ __forceinline__ void st_mc_v4(uint64_t addr, uint4 v) {
+  asm volatile("multimem.st.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(__uint_as_float(v.x)),
+               "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
                : "memory");
+}
+// A finished box of `rows` staged rows (row pitch `row_bytes`, a multiple of 16) leaves for an NVLS
+// multicast image in coalesced 16-byte stores by the whole warp; `valid_bytes` (a multiple of 16)
+// clips the last strip of a row.
+__device__ __forceinline__ void mc_store_box(const uint8_t* buf, int rows, int row_bytes, int valid_bytes,
+                                             uint64_t g, int64_t pitch, int lane) {
+  __syncwarp();  // the staging writes of every lane
+  for (int r = 0; r < rows; ++r)
+    for (int k = lane * 16; k < valid_bytes; k += 32 * 16)
+      st_mc_v4(g + (int64_t)r * pitch + k, *reinterpret_cast<const uint4*>(buf + r * row_bytes + k));
+  __syncwarp();  // the buffer may be written again
 }
 
 // ---- cross-GPU flags (peer-mapped or IPC-mapped global memory) ---------------------------------

@@ -240,19 +240,7 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
           r0 = lut4s(lut1, r0);
           r1 = lut4s(lut1, r1);
         }
-        if constexpr (PLAIN) {  // NVLS: one store per byte, the switch writes every GPU's copy
-          if (!halo_lane && !beyond) {
-            const uint64_t g = P.plain_dst_ptr + (int64_t)(y - 1 - P.y0) * P.plain_dst_pitch +
-                               (int64_t)xs * (P.expand ? 3 : 1) + (lane - 1) * (P.expand ? 24 : 8);
-            if (P.expand) {
-              st_mc_v2(g, __byte_perm(r0, 0, 0x1000), __byte_perm(r0, 0, 0x2211));
-              st_mc_v2(g + 8, __byte_perm(r0, 0, 0x3332), __byte_perm(r1, 0, 0x1000));
-              st_mc_v2(g + 16, __byte_perm(r1, 0, 0x2211), __byte_perm(r1, 0, 0x3332));
-            } else {
-              st_mc_v2(g, r0, r1);
-            }
-          }
-        } else {
+        {
           // halo lanes (0, 31) store into a per-warp dummy slot: no divergent branch around the stores
           uint8_t* d = halo_lane ? dummy : out_ring + ob * P.out_buf_bytes + er * out_pitch + (lane - 1) * (P.expand ? 24 : 8);
           if (P.expand) {  // kernel.cu:210 in registers: 8 gray -> 24 bytes
@@ -263,6 +251,14 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
           } else {
             *reinterpret_cast<uint2*>(d) = make_uint2(r0, r1);
           }
+        }
+        if (PLAIN && (er == 2 || u == steps - 1)) {
+          // NVLS: the box leaves in coalesced 16-byte stores to the multicast image, one store per
+          // byte, and the switch writes every GPU's copy
+          const int ec = (u - 2) / CH, px = P.expand ? 3 : 1;
+          mc_store_box(out_ring + ob * P.out_buf_bytes, er + 1, out_pitch, min(out_pitch, (P.W - xs) * px),
+                       P.plain_dst_ptr + (int64_t)(ya + ec * CH - P.y0) * P.plain_dst_pitch + (int64_t)xs * px,
+                       P.plain_dst_pitch, lane);
         }
         if (!PLAIN && (er == 2 || u == steps - 1)) {  // a box of finished rows leaves by TMA
           const int ec = (u - 2) / CH;

@@ -233,14 +233,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
 #pragma unroll
           for (int m = 0; m < 6; ++m) r[m] = lut4q(lut1, r[m]);
         }
-        if (MG && P.plain_dst_ptr) {  // NVLS: one store per byte, the switch writes every GPU's copy
-          if (!halo_lane && !beyond) {
-            const uint64_t g = P.plain_dst_ptr + (int64_t)(y - 2 - P.y0) * P.plain_dst_pitch + (int64_t)xs * 3 + (lane - 1) * 24;
-            st_mc_v2(g, r[0], r[1]);
-            st_mc_v2(g + 8, r[2], r[3]);
-            st_mc_v2(g + 16, r[4], r[5]);
-          }
-        } else {
+        {
           uint2* d = reinterpret_cast<uint2*>(halo_lane ? dummy
                                                         : out_ring + ob * P.out_buf_bytes + er * kS5OutBytes + (lane - 1) * 24);
           d[0] = make_uint2(r[0], r[1]);
@@ -265,6 +258,14 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
               g[2] = make_uint2(r[4], r[5]);
             }
           }
+        }
+        if (MG && P.plain_dst_ptr && (er == 4 || u == steps - 1)) {
+          // NVLS: the box leaves in coalesced 16-byte stores to the multicast image, one store per
+          // byte, and the switch writes every GPU's copy
+          const int ec = (u - 4) / CH;
+          mc_store_box(out_ring + ob * P.out_buf_bytes, er + 1, kS5OutBytes, min(kS5OutBytes, (P.W - xs) * 3),
+                       P.plain_dst_ptr + (int64_t)(ya + ec * CH - P.y0) * P.plain_dst_pitch + (int64_t)xs * 3,
+                       P.plain_dst_pitch, lane);
         }
         if (!(MG && P.plain_dst_ptr) && (er == 4 || u == steps - 1)) {  // a box of finished rows leaves by TMA
           const int ec = (u - 4) / CH;

@@ -193,14 +193,7 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
 #pragma unroll
           for (int m = 0; m < 6; ++m) r[m] = lut4s(lut1, r[m]);
         }
-        if (MG && P.plain_dst_ptr) {  // NVLS: one store per byte, the switch writes every GPU's copy
-          if (!halo_lane && !beyond) {
-            const uint64_t g = P.plain_dst_ptr + (int64_t)(y - 1 - P.y0) * P.plain_dst_pitch + (int64_t)xs * 3 + (lane - 1) * 24;
-            st_mc_v2(g, r[0], r[1]);
-            st_mc_v2(g + 8, r[2], r[3]);
-            st_mc_v2(g + 16, r[4], r[5]);
-          }
-        } else {
+        {
           uint2* d = reinterpret_cast<uint2*>(halo_lane ? dummy
                                                         : out_ring + ob * P.out_buf_bytes + er * kSSOutBytes + (lane - 1) * 24);
           d[0] = make_uint2(r[0], r[1]);
@@ -225,6 +218,14 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
               g[2] = make_uint2(r[4], r[5]);
             }
           }
+        }
+        if (MG && P.plain_dst_ptr && (er == CH - 1 || u == steps - 1)) {
+          // NVLS: the box leaves in coalesced 16-byte stores to the multicast image, one store per
+          // byte, and the switch writes every GPU's copy
+          const int ec = (u - 2) / CH;
+          mc_store_box(out_ring + ob * P.out_buf_bytes, er + 1, kSSOutBytes, min(kSSOutBytes, (P.W - xs) * 3),
+                       P.plain_dst_ptr + (int64_t)(ya + ec * CH - P.y0) * P.plain_dst_pitch + (int64_t)xs * 3,
+                       P.plain_dst_pitch, lane);
         }
         if (!(MG && P.plain_dst_ptr) && (er == CH - 1 || u == steps - 1)) {  // a box of finished rows leaves by TMA
           const int ec = (u - 2) / CH;

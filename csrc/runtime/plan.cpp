@@ -534,8 +534,8 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
   if (!encode_map(&src_map, src.ptr, src.pitch, (int64_t)L.W * 3, src_rows, kSweepInBytes, kSweepChunk)) return 0;
   const uint64_t dptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
   const bool plain = last && (L.flags & B2I_LAUNCH_DST_MCAST);
-  if (plain) {  // NVLS multicast image: 8-byte stores from registers, no tensor map on that address
-    if ((dptr | (uint64_t)dst.pitch) & 7) return 0;
+  if (plain) {  // NVLS multicast image: 16-byte stores from the staging buffer, no tensor map on that address
+    if (((dptr | (uint64_t)dst.pitch) & 15) || (((int64_t)L.W * seg.cout) & 15)) return 0;
     memset(&dst_map, 0, sizeof dst_map);
     P.plain_dst_ptr = dptr;
     P.plain_dst_pitch = dst.pitch;
@@ -672,8 +672,8 @@ int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0
   if (!encode_map(&src_map, src.ptr, src.pitch, (int64_t)L.W * 3, src_rows, kS5InBytes, kS5Chunk)) return 0;
   const uint64_t dptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
   const bool plain = last && (L.flags & B2I_LAUNCH_DST_MCAST);
-  if (plain) {  // NVLS multicast image: 8-byte stores from registers, no tensor map on that address
-    if ((dptr | (uint64_t)dst.pitch) & 7) return 0;
+  if (plain) {  // NVLS multicast image: 16-byte stores from the staging buffer, no tensor map on that address
+    if (((dptr | (uint64_t)dst.pitch) & 15) || (((int64_t)L.W * seg.cout) & 15)) return 0;
     memset(&dst_map, 0, sizeof dst_map);
     P.plain_dst_ptr = dptr;
     P.plain_dst_pitch = dst.pitch;
@@ -732,8 +732,8 @@ int try_sweep_sobel(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, i
   if (!encode_map(&src_map, src.ptr, src.pitch, (int64_t)L.W * 3, src_rows, kSSInBytes, kSSChunk)) return 0;
   const uint64_t dptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
   const bool plain = last && (L.flags & B2I_LAUNCH_DST_MCAST);
-  if (plain) {  // NVLS multicast image: 8-byte stores from registers, no tensor map on that address
-    if ((dptr | (uint64_t)dst.pitch) & 7) return 0;
+  if (plain) {  // NVLS multicast image: 16-byte stores from the staging buffer, no tensor map on that address
+    if (((dptr | (uint64_t)dst.pitch) & 15) || (((int64_t)L.W * seg.cout) & 15)) return 0;
     memset(&dst_map, 0, sizeof dst_map);
     P.plain_dst_ptr = dptr;
     P.plain_dst_pitch = dst.pitch;
