@@ -25,7 +25,7 @@ struct Options {
               backend = "auto", order = "bgr", synth, batch, outdir = ".";
   int width = 0, height = 0, channels = 3, gpus = 1, ranks = 0, root = 0, iters = 1;
   bool json = false, verbose = false, seams = false, topology = false, no_tma = false,
-       naive = false, help = false, resident = false;
+       naive = false, help = false, resident = false, replicate = false;
 };
 
 void usage() {
@@ -47,7 +47,9 @@ void usage() {
       "  --ranks N            host workers for --backend host\n"
       "  --seams              host backend: filter bands in isolation like the reference\n"
       "  --root G             GPU that owns input and output (default 0)\n"
-      "  --iters K            timed repetitions\n"
+      "  --iters K            timed repetitions (with --resident: passes of the chain over resident bands)\n"
+      "  --resident           bands stay on their GPUs, halos are pushed by the kernels\n"
+      "  --replicate          the result ends on every GPU (NVLS multicast), not on the root only\n"
       "  --no-tma             force the plain ld/st tile loaders\n"
       "  --topology           print the GPU / NVLink topology as JSON and exit\n"
       "  --json               one JSON line with timings instead of the reference-style text\n"
@@ -97,6 +99,7 @@ int main(int argc, char** argv) {
     else if (a == "--iters") o.iters = atoi(next("--iters"));
     else if (a == "--seams") o.seams = true;
     else if (a == "--resident") o.resident = true;
+    else if (a == "--replicate") o.replicate = true;
     else if (a == "--no-tma") o.no_tma = true;
     else if (a == "--topology") o.topology = true;
     else if (a == "--json") o.json = true;
@@ -261,11 +264,11 @@ int main(int argc, char** argv) {
   } else if (backend == "cuda" || backend == "naive") {
     const int flags = (o.no_tma ? B2I_LAUNCH_NO_TMA : 0) | (backend == "naive" ? B2I_LAUNCH_NAIVE : 0);
     int rc;
-    if (n <= 1 && !o.resident)
+    if (n <= 1 && !o.resident && !o.replicate)
       rc = b2i_cuda_run_host_image(&chain, img, W, H, C, (size_t)W * C, out.data(),
                                    (size_t)W * out_c, o.root, o.iters, flags, &kernel_ms, &total_ms);
     else
-      rc = b2i_ctx_run_cli(n, o.root, &chain, img, W, H, C, out.data(), o.iters, flags, o.resident,
+      rc = b2i_ctx_run_cli(n, o.root, &chain, img, W, H, C, out.data(), o.iters, flags, o.replicate ? 2 : o.resident,
                            &kernel_ms, &total_ms, report.data(), report.size());
     if (rc != B2I_OK) return fail("cuda backend");
   } else {

@@ -667,6 +667,9 @@ extern "C" int b2i_ctx_run_cli(int gpus, int root, const b2i_chain_t* chain, con
   b2i_plan_t* plan = nullptr;
   int rc = b2i_plan_create(chain, C, &plan);
   std::vector<double> per(gpus, 0.0);
+  const bool replicate = resident == 2;  // ROOT mode with the result on every GPU (NVLS multicast)
+  if (replicate) resident = 0;
+  if (rc == B2I_OK && replicate) rc = b2i_ctx_set_replicated(c, 1);
   if (rc == B2I_OK) rc = b2i_ctx_load_root(c, src, W, H, C, (size_t)W * C, out_c);
   const char* sync_env = getenv("B200IMG_SYNC");
   const int use_flags = sync_env && !strcmp(sync_env, "flags");
@@ -679,9 +682,20 @@ extern "C" int b2i_ctx_run_cli(int gpus, int root, const b2i_chain_t* chain, con
     }
   }
   if (rc == B2I_OK) rc = b2i_ctx_fetch_root(c, dst, (size_t)W * out_c);
+  int replicas_equal = -1;
+  if (rc == B2I_OK && replicate) {  // every GPU's copy must be the root's
+    std::vector<uint8_t> other((size_t)W * out_c * H);
+    replicas_equal = 1;
+    for (int g = 0; g < gpus && rc == B2I_OK; ++g) {
+      rc = b2i_ctx_fetch_replica(c, g, other.data(), (size_t)W * out_c);
+      if (rc == B2I_OK && memcmp(other.data(), dst, other.size()) != 0) replicas_equal = 0;
+    }
+  }
   if (report && report_len > 0) {
     std::string s = "{\"mode\": \"";
-    s += resident ? (use_flags ? "resident/flags" : "resident/events") : "root";
+    s += resident ? (use_flags ? "resident/flags" : "resident/events")
+                  : replicate ? (b2i_ctx_replicated(c) == 2 ? "root/replicated-nvls" : "root/replicated-plain") : "root";
+    if (replicate) s += std::string("\", \"replicas_identical\": \"") + (replicas_equal == 1 ? "yes" : "no");
     s += "\", \"gpus\": " + std::to_string(gpus) + ", \"per_gpu_ms\": [";
     char tmp[64];
     for (int i = 0; i < gpus; ++i) {

@@ -283,6 +283,8 @@ int b2i_ctx_run_resident(b2i_ctx_t* ctx, b2i_plan_t* plan, int passes, int flags
 int b2i_ctx_run_direct(b2i_ctx_t* ctx, b2i_plan_t* plan, const uint8_t* src, int W, int H, int C,
                        size_t src_pitch, uint8_t* dst, size_t dst_pitch, int flags,
                        double* total_ms);
+/* The CLI's multi-GPU run. resident: 0 = ROOT mode, 1 = RESIDENT mode (iters = passes), 2 = ROOT
+ * mode with replicated output (every GPU's copy is compared with the root's). */
 int b2i_ctx_run_cli(int gpus, int root, const b2i_chain_t* chain, const uint8_t* src, int W, int H,
                     int C, uint8_t* dst, int iters, int flags, int resident, double* kernel_ms,
                     double* total_ms, char* report, size_t report_len);

@@ -81,6 +81,12 @@ def test_cuda_backend_single_and_multi_band(tmp_path):
                            cwd=tmp_path, capture_output=True, text=True)
         assert r.returncode == 0, r.stderr + r.stdout
         assert np.array_equal(b2.read_image(str(tmp_path / "o.ppm")), want), extra
+    r = subprocess.run([_exe(), "--input", "in.ppm", "--output", "o2.ppm", "--backend", "cuda", "-np", "2",
+                        "--replicate", "--json"], cwd=tmp_path, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr + r.stdout
+    rep = json.loads(r.stdout)["runtime"]
+    assert rep["mode"].startswith("root/replicated") and rep["replicas_identical"] == "yes", rep
+    assert np.array_equal(b2.read_image(str(tmp_path / "o2.ppm")), want)
     r = subprocess.run([_exe(), "--topology"], capture_output=True, text=True)
     assert r.returncode == 0 and len(json.loads(r.stdout)["devices"]) >= 1
 
