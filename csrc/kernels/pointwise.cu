@@ -172,19 +172,6 @@ pointwise_kernel(const __grid_constant__ PointwiseParams P) {
         scalar_px<CIN, GRAY, EXPAND>(P, srow + i * CIN, drow + i * COUT, lut0, lut1);
     }
   }
-  // gather completion: the last CTA to finish releases the root's flag
-  if (P.done_flag) {
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      uint32_t* counters = reinterpret_cast<uint32_t*>(P.counters);
-      if (atomicAdd(&counters[3], 1u) + 1 == gridDim.x) {
-        atomicExch(&counters[3], 0u);
-        __threadfence_system();
-        st_release_sys(reinterpret_cast<uint32_t*>(P.done_flag), P.signal_epoch);
-      }
-    }
-  }
 }
 
 }  // namespace

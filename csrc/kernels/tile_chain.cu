@@ -583,7 +583,7 @@ __device__ void store_tile_generic(const TileParams& P, const Tile& T, const uin
 // their TMA store has read the staging buffer. (The first version fenced after every tile: a
 // membar.sys per tile on thread 0 cost ~35 us per pass at N = 2.)
 __device__ __forceinline__ bool tile_publishes(const TileParams& P, const Tile& T) {
-  return P.done_flag != 0 || (P.signal_up_flag && T.ty0 < P.y0 + P.push_rows) ||
+  return (P.signal_up_flag && T.ty0 < P.y0 + P.push_rows) ||
          (P.signal_dn_flag && T.ty0 + P.th > P.y1 - P.push_rows);
 }
 
@@ -600,11 +600,6 @@ __device__ __forceinline__ void publish_flags(const TileParams& P, const Tile& T
     if (atomicAdd(&counters[1], 1u) + 1 == (uint32_t)n_push_dn) {
       atomicExch(&counters[1], 0u);
       st_release_sys(reinterpret_cast<uint32_t*>(P.signal_dn_flag), P.signal_epoch);
-    }
-  if (P.done_flag)
-    if (atomicAdd(&counters[2], 1u) + 1 == (uint32_t)P.n_tiles) {
-      atomicExch(&counters[2], 0u);
-      st_release_sys(reinterpret_cast<uint32_t*>(P.done_flag), P.signal_epoch);
     }
 }
 

@@ -92,7 +92,6 @@ struct TileParams {
   // cross-GPU flags (0 = unused)
   uint64_t wait_up_flag, wait_dn_flag;      // local flags to reach `wait_epoch` before ghost rows are read
   uint64_t signal_up_flag, signal_dn_flag;  // neighbours' flags to set to `signal_epoch` after the pushes
-  uint64_t done_flag;                       // flag (e.g. on the root GPU) set to signal_epoch when all tiles are stored
   uint64_t counters;                        // 4 x u32 scratch in local memory, zero before launch
   uint64_t status;                          // u32 in local memory: nonzero = a wait timed out
   uint32_t wait_epoch, signal_epoch;
@@ -118,8 +117,6 @@ struct PointwiseParams {
   int32_t vec_ok;             // 16-byte path usable (pitches and bases aligned)
   int64_t src_pitch, dst_pitch;
   uint64_t src_ptr, dst_ptr;  // row 0 of the rows to process
-  uint64_t done_flag, counters;
-  uint32_t signal_epoch, pad;
   uint8_t lut0[256], lut1[256];
 };
 

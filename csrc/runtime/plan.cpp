@@ -906,7 +906,6 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
   if (last) {
     P.signal_up_flag = L.signal_up_flag;
     P.signal_dn_flag = L.signal_dn_flag;
-    P.done_flag = 0;  // completion flags: the sweep kernels fuse them, b2i_cuda_run follows up otherwise
     P.signal_epoch = L.signal_epoch;
     if (L.push_rows > 0 && (L.push_up.ptr || L.push_dn.ptr)) {
       B2I_CHECK_ARG(L.push_rows <= y1 - y0 && L.push_rows <= kGhostRows,
@@ -943,7 +942,7 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
       }
     }
   }
-  if (P.wait_up_flag || P.wait_dn_flag || P.signal_up_flag || P.signal_dn_flag || P.done_flag) {
+  if (P.wait_up_flag || P.wait_dn_flag || P.signal_up_flag || P.signal_dn_flag) {
     B2I_CHECK_ARG(L.counters && L.status, "flag use needs the counters and status scratch words");
     P.counters = L.counters;
     P.status = L.status;
@@ -979,7 +978,7 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
 }
 
 int launch_pointwise_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
-                             int y1, const b2i_view_t& src, const b2i_view_t& dst, bool last) {
+                             int y1, const b2i_view_t& src, const b2i_view_t& dst) {
   int dev = 0, sms = 0;
   B2I_CUDA(cudaGetDevice(&dev));
   B2I_TRY(device_sms(dev, &sms));
@@ -1014,12 +1013,6 @@ int launch_pointwise_segment(b2i_plan* plan, const Segment& seg, const b2i_launc
   P.dst_ptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
   P.vec_ok = !((P.src_ptr | P.dst_ptr | (uint64_t)P.src_pitch | (uint64_t)P.dst_pitch) & 15) &&
              !env_int("B200IMG_NO_VEC", 0);
-  if (false && last && L.done_flag) {
-    B2I_CHECK_ARG(L.counters, "done_flag needs the counters scratch words");
-    P.done_flag = 0;  // completion flags: the sweep kernels fuse them, b2i_cuda_run follows up otherwise
-    P.counters = L.counters;
-    P.signal_epoch = L.signal_epoch;
-  }
   const long long units = (long long)((L.W + 511) / 512) * P.rows;  // one warp per 512-pixel run
   const long long want = (units + 7) / 8;
   const int grid = (int)std::max(1LL, std::min(want, (long long)sms * 8));
@@ -1149,7 +1142,7 @@ extern "C" int b2i_cuda_run(b2i_plan_t* plan, const b2i_launch_t* Lp) {
       B2I_CHECK_ARG(out.pitch >= (int64_t)L.W * seg.cout, "tmp pitch too small");
     }
     if (last) g_wait_done_fused = false;
-    if (seg.pointwise) B2I_TRY(launch_pointwise_segment(plan, seg, L, ya, yb, cur, out, last));
+    if (seg.pointwise) B2I_TRY(launch_pointwise_segment(plan, seg, L, ya, yb, cur, out));
     else B2I_TRY(launch_tile_segment(plan, seg, L, ya, yb, cur, out, s == 0, last));
     cur = out;
     if (last && L.done_flag && !g_wait_done_fused)  // kernels without the fused flags: one-thread kernels follow

@@ -180,7 +180,8 @@ typedef struct b2i_launch {
   uint32_t wait_epoch, signal_epoch;
   uint64_t wait_up_flag, wait_dn_flag;     /* u32 flags in local memory */
   uint64_t signal_up_flag, signal_dn_flag; /* u32 flags in the neighbours' memory */
-  uint64_t done_flag;                      /* u32 flag (root GPU): set when every row is stored */
+  uint64_t done_flag;                      /* u32 flag (root GPU): set to signal_epoch when every row is stored
+                                              (by the last warp of a sweep kernel, else by a one-thread kernel) */
   uint64_t counters;                       /* 16 zeroed bytes of local device memory (flag bookkeeping); with
                                               B2I_LAUNCH_NAIVE or images under 17 pixels: 256*B2I_MAX_OPS bytes
                                               that receive the LUTs of the per-op kernels */
