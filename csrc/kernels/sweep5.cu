@@ -47,30 +47,40 @@ __device__ __forceinline__ uint32_t ev(uint32_t w) { return __byte_perm(w, 0u, 0
 __device__ __forceinline__ uint32_t od(uint32_t w) { return __byte_perm(w, 0u, 0x4341); }  // bytes 1,3 -> lanes
 
 // Horizontal taps for own word M (bytes 4M..4M+3 of the lane): even-lane and odd-lane sums.
-template <int M>
-__device__ __forceinline__ void hword(const uint32_t (&a)[10], const int (&w)[5], bool five, uint32_t& e,
-                                      uint32_t& o) {
+// FIVE: 5 taps (else the 3 in the middle); BINOM: the taps are 1 4 6 4 1 resp. 1 2 1 (the Gaussians),
+// which turns most multiplies into adds.
+template <int M, bool FIVE, bool BINOM>
+__device__ __forceinline__ void hword(const uint32_t (&a)[10], const int (&w)[5], uint32_t& e, uint32_t& o) {
   constexpr int B = 8 + 4 * M;
   const uint32_t s1 = win40<B - 3>(a), s2 = win40<B>(a), s3 = win40<B + 3>(a);
-  e = ev(s1) * w[1] + ev(s2) * w[2] + ev(s3) * w[3];
-  o = od(s1) * w[1] + od(s2) * w[2] + od(s3) * w[3];
-  if (five) {  // warp-uniform: a 3-tap kernel has w[0] == w[4] == 0
+  if constexpr (FIVE) {
     const uint32_t s0 = win40<B - 6>(a), s4 = win40<B + 6>(a);
-    e += ev(s0) * w[0] + ev(s4) * w[4];
-    o += od(s0) * w[0] + od(s4) * w[4];
+    if constexpr (BINOM) {
+      e = ev(s2) * 6u + (ev(s0) + ev(s4)) + ((ev(s1) + ev(s3)) << 2);
+      o = od(s2) * 6u + (od(s0) + od(s4)) + ((od(s1) + od(s3)) << 2);
+    } else {
+      e = ev(s0) * w[0] + ev(s1) * w[1] + ev(s2) * w[2] + ev(s3) * w[3] + ev(s4) * w[4];
+      o = od(s0) * w[0] + od(s1) * w[1] + od(s2) * w[2] + od(s3) * w[3] + od(s4) * w[4];
+    }
+  } else if constexpr (BINOM) {
+    e = ev(s1) + ev(s3) + (ev(s2) << 1);
+    o = od(s1) + od(s3) + (od(s2) << 1);
+  } else {
+    e = ev(s1) * w[1] + ev(s2) * w[2] + ev(s3) * w[3];
+    o = od(s1) * w[1] + od(s2) * w[2] + od(s3) * w[3];
   }
 }
 
-// acc (+)= h * w over the 12 lane words of a row.
+// acc (+)= h * w over the 12 lane words of a row; a set starts from the rounding bias.
 template <bool INIT>
-__device__ __forceinline__ void vacc(uint32_t (&acc)[12], const uint32_t (&h)[12], uint32_t w) {
+__device__ __forceinline__ void vacc(uint32_t (&acc)[12], const uint32_t (&h)[12], uint32_t w, uint32_t bias2) {
 #pragma unroll
-  for (int i = 0; i < 12; ++i) acc[i] = INIT ? h[i] * w : acc[i] + h[i] * w;
+  for (int i = 0; i < 12; ++i) acc[i] = (INIT ? bias2 : acc[i]) + h[i] * w;
 }
 
 // MG: the multi-GPU hooks (neighbour flags, halo pushes, NVLS multicast output) are compiled in.
 // The single-GPU instantiation carries none of them.
-template <bool MG>
+template <bool MG, bool FIVE, bool BINOM>
 __global__ void __launch_bounds__(kS5Warps * 32, kS5CtasPerSm)
 sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CUtensorMap src_map,
               const __grid_constant__ CUtensorMap dst_map) {
@@ -99,9 +109,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
     wh[i] = P.wh[i];
     wv[i] = P.wv[i];
   }
-  const bool five = (P.wh[0] | P.wh[4]) != 0;
   const uint32_t bias2 = (uint32_t)P.bias * 0x00010001u;
-  const int shift = P.shift;
   const bool reflect = P.border == B2I_BORDER_REFLECT101, replicate = P.border == B2I_BORDER_REPLICATE;
 
   uint32_t n_in = 0, n_out = 0;  // boxes consumed / stored by this warp so far
@@ -189,12 +197,12 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
         }
       }
       uint32_t h[12];
-      hword<0>(a, wh, five, h[0], h[1]);
-      hword<1>(a, wh, five, h[2], h[3]);
-      hword<2>(a, wh, five, h[4], h[5]);
-      hword<3>(a, wh, five, h[6], h[7]);
-      hword<4>(a, wh, five, h[8], h[9]);
-      hword<5>(a, wh, five, h[10], h[11]);
+      hword<0, FIVE, BINOM>(a, wh, h[0], h[1]);
+      hword<1, FIVE, BINOM>(a, wh, h[2], h[3]);
+      hword<2, FIVE, BINOM>(a, wh, h[4], h[5]);
+      hword<3, FIVE, BINOM>(a, wh, h[6], h[7]);
+      hword<4, FIVE, BINOM>(a, wh, h[8], h[9]);
+      hword<5, FIVE, BINOM>(a, wh, h[10], h[11]);
       // multipliers of this row for the output rows y+2 (k0) .. y-2 (k4). A row that also stands
       // for a mirrored / replicated row outside the image simply weighs more (warp-uniform).
       int k0 = wv[0], k1 = wv[1], k2 = wv[2], k3 = wv[3], k4 = wv[4];
@@ -209,11 +217,17 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
           if (y == P.H - 1) { k2 += wv[3] + wv[4]; k3 += wv[4]; }
         }
       }
-      vacc<true>(K0, h, (uint32_t)k0);
-      vacc<false>(K1, h, (uint32_t)k1);
-      vacc<false>(K2, h, (uint32_t)k2);
-      vacc<false>(K3, h, (uint32_t)k3);
-      vacc<false>(K4, h, (uint32_t)k4);
+      if constexpr (FIVE) {
+        vacc<true>(K0, h, (uint32_t)k0, bias2);
+        vacc<false>(K1, h, (uint32_t)k1, bias2);
+        vacc<false>(K2, h, (uint32_t)k2, bias2);
+        vacc<false>(K3, h, (uint32_t)k3, bias2);
+        vacc<false>(K4, h, (uint32_t)k4, bias2);
+      } else {  // 3 taps: the outer multipliers are zero; the set of row y+1 starts here, K4 is long complete
+        vacc<true>(K1, h, (uint32_t)k1, bias2);
+        vacc<false>(K2, h, (uint32_t)k2, bias2);
+        vacc<false>(K3, h, (uint32_t)k3, bias2);
+      }
       // ---- output row y-2 (index e = u-4 of the task) is complete --------------------------------
       if (u >= 4) {
         constexpr int er = (q + 1) % 5;  // row of the store box
@@ -225,9 +239,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
         uint32_t r[6];
 #pragma unroll
         for (int m = 0; m < 6; ++m) {
-          const uint32_t e = K4[2 * m] + bias2, o = K4[2 * m + 1] + bias2;
-          r[m] = shift == 8 ? __byte_perm(e, o, 0x7351)
-                            : (((e >> shift) & 0x00FF00FFu) | (((o >> shift) & 0x00FF00FFu) << 8));
+          r[m] = __byte_perm(K4[2 * m], K4[2 * m + 1], 0x7351);  // >> 8 (the planner scales the taps to 256) and narrow
         }
         if (P.has_lut1) {
 #pragma unroll
@@ -331,17 +343,24 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
 
 cudaError_t launch_sweep5(const Sweep5Params& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
                           int grid, cudaStream_t stream) {
-  static bool configured[64][2] = {{false}};
+  static bool configured[64][8] = {{false}};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   const bool mg = P.push_rows || P.wait_up_flag || P.wait_dn_flag || P.signal_up_flag || P.signal_dn_flag ||
                   P.plain_dst_ptr;
-  auto kern = mg ? sweep5_kernel<true> : sweep5_kernel<false>;
-  if (dev < 64 && !configured[dev][mg]) {
+  const bool five = (P.wh[0] | P.wh[4]) != 0;
+  const int variant = (mg ? 4 : 0) + (five ? 2 : 0) + (P.binom ? 1 : 0);
+  using Kern = void (*)(Sweep5Params, CUtensorMap, CUtensorMap);
+  static const Kern table[8] = {
+      sweep5_kernel<false, false, false>, sweep5_kernel<false, false, true>, sweep5_kernel<false, true, false>,
+      sweep5_kernel<false, true, true>,   sweep5_kernel<true, false, false>, sweep5_kernel<true, false, true>,
+      sweep5_kernel<true, true, false>,   sweep5_kernel<true, true, true>};
+  const Kern kern = table[variant];
+  if (dev < 64 && !configured[dev][variant]) {
     e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     if (e != cudaSuccess) return e;
-    configured[dev][mg] = true;
+    configured[dev][variant] = true;
   }
   kern<<<grid, kS5Warps * 32, P.warp_smem * kS5Warps, stream>>>(P, src_map, dst_map);
   return cudaGetLastError();

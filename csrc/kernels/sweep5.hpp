@@ -18,7 +18,8 @@ struct Sweep5Params {
   int32_t src_y_begin;       // global row of row 0 of the source tensor map
   int32_t n_strips, seg_rows, n_tasks;
   int32_t border;            // REFLECT101, REPLICATE or ZERO (REF goes to the tile kernel)
-  int32_t shift, bias;       // result = (sum + bias) >> shift
+  int32_t bias;              // result = (sum + bias) >> 8: the planner scales the vertical taps so that all taps sum to 256
+  int32_t binom;             // the horizontal taps are 1 4 6 4 1 (or 1 2 1): adds and shifts instead of multiplies
   int32_t has_lut1;          // LUT applied to the result bytes
   int32_t warp_smem, in_stage_bytes, out_buf_bytes;
   int32_t wh[5], wv[5];      // horizontal / vertical taps (a 3-tap kernel has zeros at both ends)

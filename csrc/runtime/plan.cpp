@@ -655,15 +655,20 @@ int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0
   P.y1 = y1;
   P.src_y_begin = src.y_begin;
   P.border = ph.border;
-  P.shift = pv.shift;
-  P.bias = pv.bias;
+  // the kernel narrows with a fixed >> 8: scale the vertical taps (and the bias) so that all taps
+  // sum to 256; lanes stay below 65536 (255 * 256 + bias)
+  const int up = 8 - pv.shift;
+  if (up < 0) return 0;
+  P.bias = pv.bias << up;
   P.has_lut1 = pv.lut >= 0;
   if (pv.lut >= 0) memcpy(P.lut1, seg.luts[pv.lut], 256);
   const int off = ph.ksize == 5 ? 0 : 1;  // a 3-tap kernel sits in the middle of the five slots
   for (int i = 0; i < ph.ksize; ++i) {
     P.wh[i + off] = ph.sep[i];
-    P.wv[i + off] = pv.sep[i];
+    P.wv[i + off] = pv.sep[i] << up;
   }
+  static const int b5[5] = {1, 4, 6, 4, 1}, b3[5] = {0, 1, 2, 1, 0};
+  P.binom = !memcmp(P.wh, b5, sizeof b5) || !memcmp(P.wh, b3, sizeof b3);
   P.in_stage_bytes = align_up(kS5Chunk * kS5InBytes, 128);
   P.out_buf_bytes = align_up(kS5Chunk * kS5OutBytes, 128);
   P.warp_smem = kS5Stages * P.in_stage_bytes + 2 * P.out_buf_bytes + 128;
