@@ -33,15 +33,19 @@ __device__ __forceinline__ uint32_t lut4s(const uint8_t* lut, uint32_t w) {
   return pack4_lo(a, b, c, d);
 }
 
-// Bytes [O, O+4) of the 32-byte window {left5, own0..own5, right0}.
-template <int O>
-__device__ __forceinline__ uint32_t win32(const uint32_t (&a)[8]) {
-  static_assert(O >= 0 && O <= 28, "window outside the row registers");
-  if constexpr ((O & 3) == 0) return a[O >> 2];
-  else return __funnelshift_r(a[O >> 2], a[(O >> 2) + 1], (O & 3) * 8);
+// The lane pair (x[J], x[J+2]) of the 32-byte window x = {left5, own0..own5, right0}: the two bytes a
+// tap at byte offset J contributes to the even (or, at J+1, odd) lanes of a word. Written per residue
+// of J so that every pair is extracted once per row and shared by the taps that use it.
+template <int J>
+__device__ __forceinline__ uint32_t pair_at(const uint32_t (&a)[8]) {
+  static_assert(J >= 0 && J + 2 < 32, "pair outside the row registers");
+  if constexpr ((J & 3) == 0) return __byte_perm(a[J >> 2], 0u, 0x4240);
+  else if constexpr ((J & 3) == 1) return __byte_perm(a[J >> 2], 0u, 0x4341);
+  else {
+    const uint32_t h = __funnelshift_r(a[J >> 2], a[(J >> 2) + 1], 16);  // bytes 4k+2 .. 4k+5
+    return __byte_perm(h, 0u, (J & 3) == 2 ? 0x4240 : 0x4341);
+  }
 }
-__device__ __forceinline__ uint32_t ev(uint32_t w) { return __byte_perm(w, 0u, 0x4240); }  // bytes 0,2 -> lanes
-__device__ __forceinline__ uint32_t od(uint32_t w) { return __byte_perm(w, 0u, 0x4341); }  // bytes 1,3 -> lanes
 
 // |v - 1024| + 1024 per lane, for lanes in [4, 2044]
 __device__ __forceinline__ uint32_t abs_biased(uint32_t v) { return __vmaxu2(v, 0x08000800u - v); }
@@ -165,12 +169,13 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
       auto word = [&](auto mc) {
         constexpr int M = decltype(mc)::value;
         constexpr int B = 4 + 4 * M;
-        const uint32_t sl = win32<B - 3>(a), sc = a[1 + M], sr = win32<B + 3>(a);
+        const uint32_t pl[2] = {pair_at<B - 3>(a), pair_at<B - 2>(a)}, pc[2] = {pair_at<B>(a), pair_at<B + 1>(a)},
+                       pr[2] = {pair_at<B + 3>(a), pair_at<B + 4>(a)};
         uint32_t res[2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           const int i = 2 * M + h;
-          const uint32_t l = h ? od(sl) : ev(sl), cc = h ? od(sc) : ev(sc), rr = h ? od(sr) : ev(sr);
+          const uint32_t l = pl[h], cc = pc[h], rr = pr[h];
           const uint32_t d = rr - l, s = l + rr + 2 * cc;
           const uint32_t gx = PA[i] + d * m3;
           const uint32_t gy = s * ka + kBias + S1[i] * kb + S2[i] * kc;
