@@ -82,10 +82,11 @@ __device__ __forceinline__ void gray8(const uint8_t* s, const GrayRefCoef& gk, i
 
 // PLAIN: result rows leave by 8-byte stores from registers (NVLS multicast output) instead of the
 // staging buffer + TMA store; a separate instantiation, so the single-GPU kernel pays nothing.
-// SPEC: the reference's own shape is compiled in (border=ref, no rescale, no LUT after the stencil,
-// gray -> BGR expand): the warp-uniform tests of those launch parameters, ~10 % of the row loop's
-// instructions, disappear. Everything else runs the generic instantiation.
-template <int GRAY, bool LUT0, bool PLAIN, bool SPEC>
+// SPEC: the reference programs' own shapes are compiled in -- 1 = kernel.cu (border=ref), 2 = kern.cpp
+// (border=reflect101), both without rescale, without a LUT after the stencil, with the gray -> BGR
+// expand: the warp-uniform tests of those launch parameters, ~10 % of the row loop's instructions,
+// disappear. 0 = everything else, decided at run time.
+template <int GRAY, bool LUT0, bool PLAIN, int SPEC>
 __global__ void __launch_bounds__(kWarps * 32, kSweepCtasPerSm)
 sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUtensorMap src_map,
               const __grid_constant__ CUtensorMap dst_map) {
@@ -106,7 +107,7 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
   }
   __syncthreads();  // the only block-wide barrier of the kernel
 
-  const bool expand = SPEC || P.expand;
+  const bool expand = SPEC != 0 || P.expand;
   const int out_pitch = expand ? kSweepOutBytes : kSweepStrip;  // staged bytes per output row
   uint8_t* in_ring = smem + warp * P.warp_smem;        // NST stages of CH rows x kSweepInBytes (128 B aligned)
   uint8_t* out_ring = in_ring + NST * P.in_stage_bytes;  // 2 staging buffers of CH rows x out_pitch
@@ -116,9 +117,10 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
   const GrayRefCoef gk = gray_ref_coef(P.rgb_order);
   const int rgb = P.rgb_order;
   const uint32_t w0 = P.wpk[0], w1 = P.wpk[1], w2 = P.wpk[2];
-  const bool ref = SPEC || P.border == B2I_BORDER_REF;
-  const bool scale = !SPEC && (P.shift | P.bias) != 0;
-  const bool lut1_on = !SPEC && P.has_lut1;
+  const bool ref = SPEC == 1 || (SPEC == 0 && P.border == B2I_BORDER_REF);
+  const bool reflect = SPEC == 2 || (SPEC == 0 && P.border == B2I_BORDER_REFLECT101);
+  const bool scale = SPEC == 0 && (P.shift | P.bias) != 0;
+  const bool lut1_on = SPEC == 0 && P.has_lut1;
 
   uint32_t n_in = 0;   // input chunks consumed by this warp so far (stage = n_in % NST)
   uint32_t n_out = 0;  // output chunks stored so far (buffer = n_out & 1)
@@ -156,7 +158,7 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
       }
     }
     const bool left_edge = x0 == 0, right_edge = x0 + 8 == P.W, beyond = x0 < 0 || x0 >= P.W;
-    const bool folds = !SPEC && (P.border == B2I_BORDER_REFLECT101 || P.border == B2I_BORDER_REPLICATE);
+    const bool folds = SPEC == 2 || (SPEC == 0 && (reflect || P.border == B2I_BORDER_REPLICATE));
     const bool edge_fix = folds && (xs == 0 || xs + kSweepStrip >= P.W);         // warp-uniform
     const bool vert_fix = folds && (ya <= 1 || yb >= P.H - 1);                   // warp-uniform
 
@@ -192,7 +194,7 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
       a[0] = __shfl_up_sync(0xFFFFFFFFu, a[2], 1);
       a[3] = __shfl_down_sync(0xFFFFFFFFu, a[1], 1);
       if (edge_fix) {
-        if (P.border == B2I_BORDER_REFLECT101) {  // pixel -1 := pixel 1, pixel W := pixel W-2
+        if (reflect) {  // pixel -1 := pixel 1, pixel W := pixel W-2
           if (left_edge) a[0] = __byte_perm(a[0], a[1], 0x5210);
           if (right_edge) a[3] = __byte_perm(a[3], a[2], 0x3216);
         } else {                                  // replicate: pixel -1 := pixel 0, pixel W := pixel W-1
@@ -207,7 +209,7 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
       taps(v, w1, B);   // middle taps of output row y
       taps_init(v, w0, Cc);  // top taps of output row y+1: this set starts here
       if (vert_fix) {   // row -1 := row 1 / row 0, row H := row H-2 / row H-1 (first / last segment only)
-        if (P.border == B2I_BORDER_REFLECT101) {
+        if (reflect) {
           if (y == 1) taps(v, w0, A);
           if (y == P.H - 1) {
             uint32_t pv[8];
@@ -314,13 +316,14 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
 
 cudaError_t launch_sweep3(const SweepParams& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
                           int grid, cudaStream_t stream) {
-  static bool configured[64][12] = {{false}};
+  static bool configured[64][16] = {{false}};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   const int smem = P.warp_smem * kSweepWarps;
-  const bool spec = !P.plain_dst_ptr && P.border == B2I_BORDER_REF && !(P.shift | P.bias) && !P.has_lut1 && P.expand;
-  const int variant = (P.gray == 1 ? 0 : 2) + (P.has_lut0 ? 1 : 0) + (P.plain_dst_ptr ? 4 : spec ? 8 : 0);
+  const bool shape = !P.plain_dst_ptr && !(P.shift | P.bias) && !P.has_lut1 && P.expand;
+  const int spec = !shape ? 0 : P.border == B2I_BORDER_REF ? 1 : P.border == B2I_BORDER_REFLECT101 ? 2 : 0;
+  const int variant = (P.gray == 1 ? 0 : 2) + (P.has_lut0 ? 1 : 0) + (P.plain_dst_ptr ? 4 : spec ? 4 + 4 * spec : 0);
   auto launch = [&](auto kern) -> cudaError_t {
     if (dev < 64 && !configured[dev][variant]) {
       cudaError_t e2 = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
@@ -331,18 +334,22 @@ cudaError_t launch_sweep3(const SweepParams& P, const CUtensorMap& src_map, cons
     return cudaGetLastError();
   };
   switch (variant) {
-    case 0: return launch(sweep3_kernel<1, false, false, false>);
-    case 1: return launch(sweep3_kernel<1, true, false, false>);
-    case 2: return launch(sweep3_kernel<2, false, false, false>);
-    case 3: return launch(sweep3_kernel<2, true, false, false>);
-    case 4: return launch(sweep3_kernel<1, false, true, false>);
-    case 5: return launch(sweep3_kernel<1, true, true, false>);
-    case 6: return launch(sweep3_kernel<2, false, true, false>);
-    case 7: return launch(sweep3_kernel<2, true, true, false>);
-    case 8: return launch(sweep3_kernel<1, false, false, true>);
-    case 9: return launch(sweep3_kernel<1, true, false, true>);
-    case 10: return launch(sweep3_kernel<2, false, false, true>);
-    default: return launch(sweep3_kernel<2, true, false, true>);
+    case 0: return launch(sweep3_kernel<1, false, false, 0>);
+    case 1: return launch(sweep3_kernel<1, true, false, 0>);
+    case 2: return launch(sweep3_kernel<2, false, false, 0>);
+    case 3: return launch(sweep3_kernel<2, true, false, 0>);
+    case 4: return launch(sweep3_kernel<1, false, true, 0>);
+    case 5: return launch(sweep3_kernel<1, true, true, 0>);
+    case 6: return launch(sweep3_kernel<2, false, true, 0>);
+    case 7: return launch(sweep3_kernel<2, true, true, 0>);
+    case 8: return launch(sweep3_kernel<1, false, false, 1>);
+    case 9: return launch(sweep3_kernel<1, true, false, 1>);
+    case 10: return launch(sweep3_kernel<2, false, false, 1>);
+    case 11: return launch(sweep3_kernel<2, true, false, 1>);
+    case 12: return launch(sweep3_kernel<1, false, false, 2>);
+    case 13: return launch(sweep3_kernel<1, true, false, 2>);
+    case 14: return launch(sweep3_kernel<2, false, false, 2>);
+    default: return launch(sweep3_kernel<2, true, false, 2>);
   }
 }
 
