@@ -11,8 +11,8 @@
 // with the last term makes both lanes non-negative again before they are looked at.
 //   gx(y-1) = D(y-2) + 2 D(y-1) + D(y)   -> one running partial sum and the previous D
 //   gy(y-1) = S(y) - S(y-2)              -> the two previous S rows, swapping roles every row
-// Mirrored / replicated rows beyond the top and bottom of the image are the same data as a real
-// row, so they only change three warp-uniform multipliers and which S rows are subtracted.
+// The mirrored / replicated row above the image is read from the box that holds its source row; the
+// one below is folded into the state once per strip. The row loop itself carries no border rules.
 #include "b200img.h"
 #include "device_utils.cuh"
 #include "sweep_sobel.hpp"
@@ -126,11 +126,13 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
       const int y = ya - 1 + u;
       uint32_t a[8];
       {
-        const uint8_t* s = stage_base + q * kSSInBytes + 8 + lane * 24;
+        // The row above the image is row 1 (reflect101) or row 0 (replicate): both sit in the same box.
+        // Rows outside the image otherwise (zero-filled by TMA) and lanes beyond the right edge give 0.
+        const bool above = vert_fix && y < 0;
+        const uint8_t* s = stage_base + (above ? (reflect ? 2 : 1) : q) * kSSInBytes + 8 + lane * 24;
         const uint2 v0 = *reinterpret_cast<const uint2*>(s), v1 = *reinterpret_cast<const uint2*>(s + 8),
                     v2 = *reinterpret_cast<const uint2*>(s + 16);
-        // rows outside the image (zero-filled by TMA) and lanes beyond the right edge contribute 0
-        const bool valid = (unsigned)y < (unsigned)P.H && !beyond;
+        const bool valid = ((unsigned)y < (unsigned)P.H || above) && !beyond;
         a[1] = valid ? v0.x : 0u; a[2] = valid ? v0.y : 0u; a[3] = valid ? v1.x : 0u;
         a[4] = valid ? v1.y : 0u; a[5] = valid ? v2.x : 0u; a[6] = valid ? v2.y : 0u;
       }
@@ -145,18 +147,20 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
           if (right_edge) a[7] = __byte_perm(a[6], 0u, 0x3321);
         }
       }
-      // warp-uniform border rules of this row (see the header comment)
-      // gx(y-1) = PA + m3 D(y), PA' = m1 D(y-1) + m2 D(y); gy(y-1) = ka S(y) + kb S(y-1) + kc S(y-2)
-      uint32_t m1 = 1, m2 = 2, m3 = 1, ka = 1, kb = 0, kc = 0xFFFFFFFFu;
-      if (vert_fix) {
-        if (reflect) {
-          if (y == P.H - 1) m1 = 2;
-          if (y == 1) { m3 = 2; ka = 0; kc = 0; }  // S(-1) := S(1), the current row
-          if (y == P.H) kc = 0;                    // S(H) := S(H-2); S(H) itself is a zero row
-        } else {
-          if (y == 0 || y == P.H - 1) m2 = 3;
-          if (y == 1) { kb = 0xFFFFFFFFu; kc = 0; }  // S(-1) := S(0)
-          if (y == P.H) kb = 1;                      // S(H) := S(H-1)
+      // The row below the image never arrives (this step sees zeros, d = s = 0): its mirror image is
+      // folded into the state instead, once per strip, so that the row loop carries no border rules.
+      //   reflect101: D(H) := D(H-2), S(H) := S(H-2)  ->  gx = 2 PA - 2 D(H-1) - bias, gy = 0
+      //   replicate:  D(H) := D(H-1), S(H) := S(H-1)  ->  gx = PA + D(H-1),           gy = S(H-1) - S(H-2)
+      if (vert_fix && y == P.H) {
+#pragma unroll
+        for (int i = 0; i < 12; ++i) {
+          if (reflect) {
+            PA[i] = 2 * PA[i] - 2 * DP[i] - kBias;
+            S2[i] = 0;
+          } else {
+            PA[i] = PA[i] + DP[i];
+            S2[i] = S2[i] - S1[i];
+          }
         }
       }
       constexpr int er = (q + 2) % CH;  // row of the store box
@@ -177,9 +181,9 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
           const int i = 2 * M + h;
           const uint32_t l = pl[h], cc = pc[h], rr = pr[h];
           const uint32_t d = rr - l, s = l + rr + 2 * cc;
-          const uint32_t gx = PA[i] + d * m3;
-          const uint32_t gy = s * ka + kBias + S1[i] * kb + S2[i] * kc;
-          PA[i] = DP[i] * m1 + kBias + d * m2;
+          const uint32_t gx = PA[i] + d;
+          const uint32_t gy = s - S2[i] + kBias;
+          PA[i] = DP[i] + kBias + 2 * d;
           DP[i] = d;
           S2[i] = s;
           res[h] = __vminu2(abs_biased(gx) + abs_biased(gy), 0x08FF08FFu);  // low byte = clamp(|gx|+|gy|)
