@@ -13,7 +13,8 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _REPO = os.path.dirname(_HERE)
-LIB_PATH = os.path.join(_HERE, "lib", "libb200img.so")
+# B200IMG_LIB points at another build of the library (A/B measurements, system-wide installs)
+LIB_PATH = os.environ.get("B200IMG_LIB") or os.path.join(_HERE, "lib", "libb200img.so")
 
 B2I_MAX_OPS = 16
 B2I_MAX_GPUS = 16
