@@ -19,6 +19,7 @@
 // Source and destination may be peer memory (scatter / gather fused), exactly as in tile_chain.cu.
 #include "b200img.h"
 #include "device_utils.cuh"
+#include "sweep_hooks.cuh"
 #include "sweep3.hpp"
 
 #include <type_traits>
@@ -301,15 +302,7 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
     n_in += n_chunks;
     n_out += (yb - ya + CH - 1) / CH;
   }
-  if (P.done_flag | P.wait_done_mask) __threadfence_system();  // every lane's plain stores before the flag
-  __syncwarp();
-  if (lane == 0) {
-    tma_store_wait_all();
-    if ((P.done_flag | P.wait_done_mask) && blockIdx.x * kWarps + warp < P.n_tasks)
-      sweep_finish(reinterpret_cast<uint32_t*>(P.counters) + 2, (uint32_t)min(total_warps, P.n_tasks), P.done_flag,
-                   P.signal_epoch, P.wait_done_flags, P.wait_done_mask, reinterpret_cast<uint32_t*>(P.status),
-                   P.timeout_ns);
-  }
+  sweep_kernel_end(P, blockIdx.x * kWarps + warp, total_warps, lane);
 }
 
 }  // namespace

@@ -19,6 +19,7 @@
 // Exact: every lane stays below 65536 (normalised non-negative kernels, checked by the planner).
 #include "b200img.h"
 #include "device_utils.cuh"
+#include "sweep_hooks.cuh"
 #include "sweep5.hpp"
 
 #include <type_traits>
@@ -138,16 +139,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
     const bool sig_up = MG && P.signal_up_flag && ya < P.y0 + P.push_rows;
     const bool sig_dn = MG && P.signal_dn_flag && yb > P.y1 - P.push_rows;
     if (lane == 0) {
-      if (MG && P.wait_up_flag && (ya - 2 < P.y0 || sig_up)) {
-        if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_up_flag), P.wait_epoch, P.timeout_ns))
-          atomicExch(reinterpret_cast<uint32_t*>(P.status), 1u);
-        asm volatile("fence.proxy.async;" ::: "memory");
-      }
-      if (MG && P.wait_dn_flag && (yb + 2 > P.y1 || sig_dn)) {
-        if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_dn_flag), P.wait_epoch, P.timeout_ns))
-          atomicExch(reinterpret_cast<uint32_t*>(P.status), 2u);
-        asm volatile("fence.proxy.async;" ::: "memory");
-      }
+      if (MG) sweep_wait_neighbours(P, ya, yb, 2, sig_up, sig_dn);
       for (int c = 0; c < min(NST, n_chunks); ++c) {
         const uint32_t st = (n_in + c) % NST;
         mbar_arrive_expect_tx(&bar[st], CH * kS5InBytes);
@@ -261,25 +253,8 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
           d[1] = make_uint2(r[2], r[3]);
           d[2] = make_uint2(r[4], r[5]);
         }
-        if (MG && P.push_rows) {  // halo rows also go straight from registers into the neighbours' ghost rows
-          const int oy = y - 2;
-          if (!halo_lane && !beyond) {
-            const int64_t col = (int64_t)xs * 3 + (lane - 1) * 24;
-            if (P.push_up_ptr && oy < P.y0 + P.push_rows) {
-              uint2* g = reinterpret_cast<uint2*>(P.push_up_ptr + (int64_t)(oy - P.y0) * P.push_pitch + col);
-              g[0] = make_uint2(r[0], r[1]);
-              g[1] = make_uint2(r[2], r[3]);
-              g[2] = make_uint2(r[4], r[5]);
-            }
-            if (P.push_dn_ptr && oy >= P.y1 - P.push_rows) {
-              uint2* g = reinterpret_cast<uint2*>(P.push_dn_ptr +
-                                                  (int64_t)(oy - (P.y1 - P.push_rows)) * P.push_pitch + col);
-              g[0] = make_uint2(r[0], r[1]);
-              g[1] = make_uint2(r[2], r[3]);
-              g[2] = make_uint2(r[4], r[5]);
-            }
-          }
-        }
+        if (MG && P.push_rows && !halo_lane && !beyond)  // halo rows also go into the neighbours' ghost rows
+          sweep_push_row(P, y - 2, (int64_t)xs * 3 + (lane - 1) * 24, r);
         if (MG && P.plain_dst_ptr && (er == 4 || u == steps - 1)) {
           // NVLS: the box leaves in coalesced 16-byte stores to the multicast image, one store per
           // byte, and the switch writes every GPU's copy
@@ -321,31 +296,9 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
     }
     n_in += n_chunks;
     n_out += (yb - ya + CH - 1) / CH;
-    if (sig_up || sig_dn) {  // count the task in; the last one releases the neighbour's flag
-      __threadfence_system();
-      __syncwarp();
-      if (lane == 0) {
-        uint32_t* counters = reinterpret_cast<uint32_t*>(P.counters);
-        if (sig_up && atomicAdd(&counters[0], 1u) + 1 == (uint32_t)P.n_up_tasks) {
-          atomicExch(&counters[0], 0u);
-          st_release_sys(reinterpret_cast<uint32_t*>(P.signal_up_flag), P.signal_epoch);
-        }
-        if (sig_dn && atomicAdd(&counters[1], 1u) + 1 == (uint32_t)P.n_dn_tasks) {
-          atomicExch(&counters[1], 0u);
-          st_release_sys(reinterpret_cast<uint32_t*>(P.signal_dn_flag), P.signal_epoch);
-        }
-      }
-    }
+    if (sig_up || sig_dn) sweep_signal_neighbours(P, sig_up, sig_dn, lane);
   }
-  if (P.done_flag | P.wait_done_mask) __threadfence_system();  // every lane's plain stores before the flag
-  __syncwarp();
-  if (lane == 0) {
-    tma_store_wait_all();
-    if ((P.done_flag | P.wait_done_mask) && blockIdx.x * kS5Warps + warp < P.n_tasks)
-      sweep_finish(reinterpret_cast<uint32_t*>(P.counters) + 2, (uint32_t)min(total_warps, P.n_tasks), P.done_flag,
-                   P.signal_epoch, P.wait_done_flags, P.wait_done_mask, reinterpret_cast<uint32_t*>(P.status),
-                   P.timeout_ns);
-  }
+  sweep_kernel_end(P, blockIdx.x * kS5Warps + warp, total_warps, lane);
 }
 
 }  // namespace
