@@ -87,7 +87,7 @@ __device__ __forceinline__ void gray8(const uint8_t* s, const GrayRefCoef& gk, i
 // (border=reflect101), both without rescale, without a LUT after the stencil, with the gray -> BGR
 // expand: the warp-uniform tests of those launch parameters, ~10 % of the row loop's instructions,
 // disappear. 0 = everything else, decided at run time.
-template <int GRAY, bool LUT0, bool PLAIN, int SPEC>
+template <int GRAY, int LUT0, bool PLAIN, int SPEC>
 __global__ void __launch_bounds__(kWarps * 32, kSweepCtasPerSm)
 sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUtensorMap src_map,
               const __grid_constant__ CUtensorMap dst_map) {
@@ -118,6 +118,9 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
   const GrayRefCoef gk = gray_ref_coef(P.rgb_order);
   const int rgb = P.rgb_order;
   const uint32_t w0 = P.wpk[0], w1 = P.wpk[1], w2 = P.wpk[2];
+  // gray8<1> returns the float bits 0x4B740000 + gray: folded into the affine table's constant
+  const uint32_t aff_a = (uint32_t)P.lut0_a, aff_c = (uint32_t)P.lut0_b - (GRAY == 1 ? aff_a * 0x4B740000u : 0u);
+  const int aff_s = P.lut0_s;
   const bool ref = SPEC == 1 || (SPEC == 0 && P.border == B2I_BORDER_REF);
   const bool reflect = SPEC == 2 || (SPEC == 0 && P.border == B2I_BORDER_REFLECT101);
   const bool scale = SPEC == 0 && (P.shift | P.bias) != 0;
@@ -184,13 +187,24 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
         // any other, then replaced by 0 (they contribute nothing; borders are folded in below)
         uint32_t g[8];
         gray8<GRAY>(stage_base + q * kSweepInBytes + 8 + lane * 24, gk, rgb, g);
-        if (LUT0) {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) g[i] = lut0[g[i] & 0xFF];
-        }
         const bool valid = (unsigned)y < (unsigned)P.H && !beyond;
-        a[1] = valid ? pack4_lo(g[0], g[1], g[2], g[3]) : 0u;
-        a[2] = valid ? pack4_lo(g[4], g[5], g[6], g[7]) : 0u;
+        if constexpr (LUT0 == 2) {
+          // the table is clamp((a v + b) >> s) (a contrast stretch, kernel.cu:56 / kern.cpp:74): one
+          // multiply-add and a shift per pixel, clamped by the saturating pack; no shared-memory
+          // lookups in the row loop. The constant absorbs the float bits gray8 leaves above the value.
+          int t[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) t[i] = (int)(g[i] * aff_a + aff_c) >> aff_s;
+          a[1] = valid ? sat_pack4(t[0], t[1], t[2], t[3]) : 0u;
+          a[2] = valid ? sat_pack4(t[4], t[5], t[6], t[7]) : 0u;
+        } else {
+          if constexpr (LUT0 == 1) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) g[i] = lut0[g[i] & 0xFF];
+          }
+          a[1] = valid ? pack4_lo(g[0], g[1], g[2], g[3]) : 0u;
+          a[2] = valid ? pack4_lo(g[4], g[5], g[6], g[7]) : 0u;
+        }
       }
       a[0] = __shfl_up_sync(0xFFFFFFFFu, a[2], 1);
       a[3] = __shfl_down_sync(0xFFFFFFFFu, a[1], 1);
@@ -309,41 +323,29 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
 
 cudaError_t launch_sweep3(const SweepParams& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
                           int grid, cudaStream_t stream) {
-  static bool configured[64][16] = {{false}};
+  static bool configured[64][24] = {{false}};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   const int smem = P.warp_smem * kSweepWarps;
   const bool shape = !P.plain_dst_ptr && !(P.shift | P.bias) && !P.has_lut1 && P.expand;
   const int spec = !shape ? 0 : P.border == B2I_BORDER_REF ? 1 : P.border == B2I_BORDER_REFLECT101 ? 2 : 0;
-  const int variant = (P.gray == 1 ? 0 : 2) + (P.has_lut0 ? 1 : 0) + (P.plain_dst_ptr ? 4 : spec ? 4 + 4 * spec : 0);
-  auto launch = [&](auto kern) -> cudaError_t {
-    if (dev < 64 && !configured[dev][variant]) {
-      cudaError_t e2 = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-      if (e2 != cudaSuccess) return e2;
-      configured[dev][variant] = true;
-    }
-    kern<<<grid, kSweepWarps * 32, smem, stream>>>(P, src_map, dst_map);
-    return cudaGetLastError();
-  };
-  switch (variant) {
-    case 0: return launch(sweep3_kernel<1, false, false, 0>);
-    case 1: return launch(sweep3_kernel<1, true, false, 0>);
-    case 2: return launch(sweep3_kernel<2, false, false, 0>);
-    case 3: return launch(sweep3_kernel<2, true, false, 0>);
-    case 4: return launch(sweep3_kernel<1, false, true, 0>);
-    case 5: return launch(sweep3_kernel<1, true, true, 0>);
-    case 6: return launch(sweep3_kernel<2, false, true, 0>);
-    case 7: return launch(sweep3_kernel<2, true, true, 0>);
-    case 8: return launch(sweep3_kernel<1, false, false, 1>);
-    case 9: return launch(sweep3_kernel<1, true, false, 1>);
-    case 10: return launch(sweep3_kernel<2, false, false, 1>);
-    case 11: return launch(sweep3_kernel<2, true, false, 1>);
-    case 12: return launch(sweep3_kernel<1, false, false, 2>);
-    case 13: return launch(sweep3_kernel<1, true, false, 2>);
-    case 14: return launch(sweep3_kernel<2, false, false, 2>);
-    default: return launch(sweep3_kernel<2, true, false, 2>);
+  const int mode = P.plain_dst_ptr ? 1 : spec ? 1 + spec : 0;  // 0 generic, 1 NVLS stores, 2 kernel.cu shape, 3 kern.cpp shape
+  const int variant = mode * 6 + (P.gray == 1 ? 0 : 3) + P.has_lut0;  // has_lut0: 0 none, 1 table, 2 affine
+  using Kern = void (*)(SweepParams, CUtensorMap, CUtensorMap);
+#define B2I_S3_ROW(PLAIN, SPEC)                                                                       \
+  sweep3_kernel<1, 0, PLAIN, SPEC>, sweep3_kernel<1, 1, PLAIN, SPEC>, sweep3_kernel<1, 2, PLAIN, SPEC>, \
+      sweep3_kernel<2, 0, PLAIN, SPEC>, sweep3_kernel<2, 1, PLAIN, SPEC>, sweep3_kernel<2, 2, PLAIN, SPEC>
+  static const Kern table[24] = {B2I_S3_ROW(false, 0), B2I_S3_ROW(true, 0), B2I_S3_ROW(false, 1), B2I_S3_ROW(false, 2)};
+#undef B2I_S3_ROW
+  const Kern kern = table[variant];
+  if (dev < 64 && !configured[dev][variant]) {
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return e;
+    configured[dev][variant] = true;
   }
+  kern<<<grid, kSweepWarps * 32, smem, stream>>>(P, src_map, dst_map);
+  return cudaGetLastError();
 }
 
 }  // namespace b2i

@@ -20,7 +20,9 @@ struct SweepParams {
   int32_t n_strips, seg_rows, n_tasks;
   int32_t gray;               // 1 = kernel.cu:39-42, 2 = cv::cvtColor
   int32_t rgb_order;
-  int32_t has_lut0, has_lut1; // LUT after the gray conversion / after the stencil
+  int32_t has_lut0, has_lut1; // LUT after the gray conversion / after the stencil; has_lut0 == 2: the table is
+                              // clamp((lut0_a * v + lut0_b) >> lut0_s), computed instead of looked up
+  int32_t lut0_a, lut0_b, lut0_s;
   int32_t border, shift, bias, expand;
   int32_t warp_smem;          // bytes of dynamic shared memory per warp
   int32_t in_stage_bytes, out_buf_bytes;  // 128-byte aligned sizes of one input stage / one staging buffer

@@ -486,6 +486,41 @@ void sweep_finish_fill(Params& P, const b2i_launch_t& L) {
   g_wait_done_fused = true;
 }
 
+// Is the table clamp((a v + b) >> s) for small integers? Contrast stretches are (kernel.cu:56 with
+// factor 3.5 is clamp((7v - 640) >> 1), kern.cpp:74 is clamp(3v - 256)); the sweep kernel then
+// computes them instead of looking them up. Exhaustive over all 256 entries, so exact.
+bool affine_lut(const uint8_t* lut, int32_t* a_out, int32_t* b_out, int32_t* s_out) {
+  for (int s = 0; s <= 4; ++s)
+    for (int a = -(64 << s); a <= (64 << s); ++a) {
+      if (a == 0) continue;
+      // b from the unsaturated entries: (a v + b) >> s == lut[v]  <=>  lut[v] << s <= a v + b < (lut[v] + 1) << s
+      long long lo = -(1LL << 40), hi = 1LL << 40;
+      bool any = false;
+      for (int v = 0; v < 256; ++v) {
+        if (lut[v] == 0 || lut[v] == 255) continue;
+        any = true;
+        lo = std::max(lo, ((long long)lut[v] << s) - (long long)a * v);
+        hi = std::min(hi, (((long long)lut[v] + 1) << s) - 1 - (long long)a * v);
+      }
+      if (!any || lo > hi) continue;
+      for (long long b = lo; b <= std::min(hi, lo + 4); ++b) {
+        bool ok = true;
+        for (int v = 0; v < 256 && ok; ++v) {
+          long long t = ((long long)a * v + b) >> s;
+          t = t < 0 ? 0 : t > 255 ? 255 : t;
+          ok = t == lut[v];
+        }
+        if (ok) {
+          *a_out = a;
+          *b_out = (int32_t)b;
+          *s_out = s;
+          return true;
+        }
+      }
+    }
+  return false;
+}
+
 int sweep_seg_rows(int n_strips, int rows, int resident, int chunk, int lo, int hi, int halo_rows);
 
 // The warp-sweep kernel (kernels/sweep3.cu) takes segments of the reference's own shape:
@@ -520,6 +555,8 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
   P.has_lut1 = st.lut >= 0;
   if (g.lut >= 0) memcpy(P.lut0, seg.luts[g.lut], 256);
   if (st.lut >= 0) memcpy(P.lut1, seg.luts[st.lut], 256);
+  if (g.lut >= 0 && !env_int("B200IMG_NO_AFFINE_LUT", 0) && affine_lut(P.lut0, &P.lut0_a, &P.lut0_b, &P.lut0_s))
+    P.has_lut0 = 2;
   P.border = st.border;
   P.shift = st.shift;
   P.bias = st.bias;
