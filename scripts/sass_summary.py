@@ -14,7 +14,7 @@ EVID = ["UTMALDG.2D", "UTMASTG.2D", "UTMACCTL.PF", "UTMACMDFLUSH", "SYNCS.ARRIVE
         "SYNCS.EXCH.64", "IDP.4A.U8.S8", "FFMA.RM", "VIMNMX.U16x2", "FENCE.VIEW.ASYNC.S", "STG.E.STRONG.SYS", "LDG.E.STRONG.SYS",
         "ST.E.STRONG.SYS", "LD.E.STRONG.SYS", "LDG.E.NA.128.CONSTANT", "STG.E.NA.128", "STG.E.64", "ST.E.64", "SHFL.UP", "SHFL.DOWN",
         "I2IP", "PRMT", "IMAD", "LDS.64", "LDS.128", "STS.64", "STS.128", "LDS.U8"]
-HOT = ("sweep3_kernel<1, true, false, 1>", "sweep5_kernel<false, true, true>", "sweep5_kernel<true, true, true>",
+HOT = ("sweep3_kernel<1, 2, false, 1>", "sweep5_kernel<false, true, true>", "sweep5_kernel<true, true, true>",
        "sweep_sobel_kernel<false>",
        "tile_chain_kernel", "pointwise_kernel<3, 1, false>", "pointwise_kernel<3, 0, false>")
 
@@ -64,7 +64,7 @@ with open(os.path.join(OUT, "SUMMARY.md"), "w") as f:
             "packed 16-bit min/max (Sobel magnitude), `*.STRONG.SYS` = system-scope flag release/acquire for cross-GPU\n"
             "ordering, `LDG/STG.E.NA.128` = streaming 16-byte accesses (also used on peer pointers), `ST(G).E.64` in the sweep\n"
             "kernels = halo pushes into the neighbours' ghost rows and NVLS multicast stores (`multimem.st` assembles to a\n"
-            "plain store; the multicast is in the address mapping). Template arguments: `sweep3_kernel<gray, lut0, plain,\n"
+            "plain store; the multicast is in the address mapping). Template arguments: `sweep3_kernel<gray, lut0 (0 none, 1 table, 2 computed), plain,\n"
             "compiled-in shape (1 = kernel.cu, 2 = kern.cpp)>`, `sweep5_kernel<multi-GPU hooks, 5 taps, binomial taps>`,\n"
             "`sweep_sobel_kernel<multi-GPU hooks>`, `pointwise_kernel<channels in, gray, expand>`.\n"
             "Full listings of the hot kernels are next to this file.\n\n"
