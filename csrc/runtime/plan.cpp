@@ -11,6 +11,8 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -64,6 +66,9 @@ struct Segment {
   uint8_t luts[kMaxLuts][256];
   int raw_fix_border = -1;
   int chan_a = 0, chan_b = 0;  // widest plane each ping-pong buffer has to hold
+  // the first phase's LUT as clamp((a v + b) >> s), if it is one (found once, at plan creation)
+  int lut0_affine = 0;
+  int32_t aff_a = 0, aff_b = 0, aff_s = 0;
   // pointwise segments
   int pw_gray = 0, pw_expand = 0, pw_has_lut0 = 0, pw_has_lut1 = 0;
   uint8_t pw_lut0[256], pw_lut1[256];
@@ -416,6 +421,49 @@ bool sweep_shape(const Segment& seg) {
          seg.phases[0].border != B2I_BORDER_REF;
 }
 
+// Is the table clamp((a v + b) >> s) for small integers? Contrast stretches are (kernel.cu:56 with
+// factor 3.5 is clamp((7v - 640) >> 1), kern.cpp:74 is clamp(3v - 256)); the sweep kernel then
+// computes them instead of looking them up. Exhaustive over all 256 entries, so exact.
+bool affine_lut(const uint8_t* lut, int32_t* a_out, int32_t* b_out, int32_t* s_out) {
+  int v1 = -1, v2 = -1;  // the unsaturated span gives the slope; only a few multipliers per shift are tried
+  for (int v = 0; v < 256; ++v)
+    if (lut[v] != 0 && lut[v] != 255) {
+      if (v1 < 0) v1 = v;
+      v2 = v;
+    }
+  if (v1 < 0 || v2 == v1) return false;
+  const double slope = ((double)lut[v2] - lut[v1]) / (v2 - v1);
+  for (int s = 0; s <= 4; ++s)
+    for (int a = (int)std::floor(slope * (1 << s)) - 1; a <= (int)std::ceil(slope * (1 << s)) + 1; ++a) {
+      if (a == 0 || a < -2048 || a > 2048) continue;
+      // b from the unsaturated entries: (a v + b) >> s == lut[v]  <=>  lut[v] << s <= a v + b < (lut[v] + 1) << s
+      long long lo = -(1LL << 40), hi = 1LL << 40;
+      bool any = false;
+      for (int v = 0; v < 256; ++v) {
+        if (lut[v] == 0 || lut[v] == 255) continue;
+        any = true;
+        lo = std::max(lo, ((long long)lut[v] << s) - (long long)a * v);
+        hi = std::min(hi, (((long long)lut[v] + 1) << s) - 1 - (long long)a * v);
+      }
+      if (!any || lo > hi) continue;
+      for (long long b = lo; b <= std::min(hi, lo + 4); ++b) {
+        bool ok = true;
+        for (int v = 0; v < 256 && ok; ++v) {
+          long long t = ((long long)a * v + b) >> s;
+          t = t < 0 ? 0 : t > 255 ? 255 : t;
+          ok = t == lut[v];
+        }
+        if (ok) {
+          *a_out = a;
+          *b_out = (int32_t)b;
+          *s_out = s;
+          return true;
+        }
+      }
+    }
+  return false;
+}
+
 // Greedy segmentation: extend the segment while the tile kernel can still absorb it. With
 // `split`, a segment the sweep kernels take is closed instead of being fused with what follows.
 int segment_chain(const std::vector<Elem>& el, int in_channels, bool split, std::vector<Segment>& out) {
@@ -449,6 +497,13 @@ int segment_chain(const std::vector<Elem>& el, int in_channels, bool split, std:
     }
     if (!have) return B2I_ERR_UNSUPPORTED;
     c = best.cout;
+    if (!best.pointwise && !best.phases.empty() && best.phases[0].lut >= 0)
+    {
+      best.lut0_affine = affine_lut(best.luts[best.phases[0].lut], &best.aff_a, &best.aff_b, &best.aff_s);
+      if (env_int("B200IMG_DEBUG", 0) & 2)
+        fprintf(stderr, "b200img: first LUT of segment %zu %s clamp((%d v + %d) >> %d)\n", out.size(),
+                best.lut0_affine ? "is" : "is not", best.aff_a, best.aff_b, best.aff_s);
+    }
     out.push_back(best);
     i = best_end;
   }
@@ -486,41 +541,6 @@ void sweep_finish_fill(Params& P, const b2i_launch_t& L) {
   g_wait_done_fused = true;
 }
 
-// Is the table clamp((a v + b) >> s) for small integers? Contrast stretches are (kernel.cu:56 with
-// factor 3.5 is clamp((7v - 640) >> 1), kern.cpp:74 is clamp(3v - 256)); the sweep kernel then
-// computes them instead of looking them up. Exhaustive over all 256 entries, so exact.
-bool affine_lut(const uint8_t* lut, int32_t* a_out, int32_t* b_out, int32_t* s_out) {
-  for (int s = 0; s <= 4; ++s)
-    for (int a = -(64 << s); a <= (64 << s); ++a) {
-      if (a == 0) continue;
-      // b from the unsaturated entries: (a v + b) >> s == lut[v]  <=>  lut[v] << s <= a v + b < (lut[v] + 1) << s
-      long long lo = -(1LL << 40), hi = 1LL << 40;
-      bool any = false;
-      for (int v = 0; v < 256; ++v) {
-        if (lut[v] == 0 || lut[v] == 255) continue;
-        any = true;
-        lo = std::max(lo, ((long long)lut[v] << s) - (long long)a * v);
-        hi = std::min(hi, (((long long)lut[v] + 1) << s) - 1 - (long long)a * v);
-      }
-      if (!any || lo > hi) continue;
-      for (long long b = lo; b <= std::min(hi, lo + 4); ++b) {
-        bool ok = true;
-        for (int v = 0; v < 256 && ok; ++v) {
-          long long t = ((long long)a * v + b) >> s;
-          t = t < 0 ? 0 : t > 255 ? 255 : t;
-          ok = t == lut[v];
-        }
-        if (ok) {
-          *a_out = a;
-          *b_out = (int32_t)b;
-          *s_out = s;
-          return true;
-        }
-      }
-    }
-  return false;
-}
-
 int sweep_seg_rows(int n_strips, int rows, int resident, int chunk, int lo, int hi, int halo_rows);
 
 // The warp-sweep kernel (kernels/sweep3.cu) takes segments of the reference's own shape:
@@ -555,8 +575,12 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
   P.has_lut1 = st.lut >= 0;
   if (g.lut >= 0) memcpy(P.lut0, seg.luts[g.lut], 256);
   if (st.lut >= 0) memcpy(P.lut1, seg.luts[st.lut], 256);
-  if (g.lut >= 0 && !env_int("B200IMG_NO_AFFINE_LUT", 0) && affine_lut(P.lut0, &P.lut0_a, &P.lut0_b, &P.lut0_s))
+  if (g.lut >= 0 && seg.lut0_affine && !env_int("B200IMG_NO_AFFINE_LUT", 0)) {
     P.has_lut0 = 2;
+    P.lut0_a = seg.aff_a;
+    P.lut0_b = seg.aff_b;
+    P.lut0_s = seg.aff_s;
+  }
   P.border = st.border;
   P.shift = st.shift;
   P.bias = st.bias;
