@@ -1,0 +1,312 @@
+// Launchers of the sweep kernels (kernels/sweep3.cu, sweep5.cu, sweep_sobel.cu): eligibility,
+// parameters, tensor maps, segment heights, multi-GPU hooks.
+#include <algorithm>
+#include <cstring>
+
+#include "plan_internal.hpp"
+
+namespace b2i {
+
+// Completion flags of ROOT mode, fused into the end of a sweep kernel (device_utils.cuh:
+// sweep_finish). Tells b2i_cuda_run that no separate wait kernel is needed.
+thread_local bool g_wait_done_fused = false;
+template <class Params>
+static void sweep_finish_fill(Params& P, const b2i_launch_t& L) {
+  P.done_flag = L.done_flag;
+  P.wait_done_flags = L.wait_done_flags;
+  P.wait_done_mask = L.wait_done_flags ? L.wait_done_mask : 0;
+  P.signal_epoch = L.signal_epoch;
+  P.counters = L.counters;
+  P.status = L.status;
+  P.timeout_ns = L.timeout_ns ? L.timeout_ns : 2000000000ull;
+  g_wait_done_fused = true;
+}
+
+static int sweep_seg_rows(int n_strips, int rows, int resident, int chunk, int lo, int hi, int halo_rows);
+
+// The warp-sweep kernel (kernels/sweep3.cu) takes segments of the reference's own shape:
+// gray (+LUT) -> one 3x3 stencil on the gray plane (+LUT, +expand). Returns 1 if it launched,
+// 0 if the segment or the buffers do not qualify (the tile-chain kernel then runs it).
+int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
+              const b2i_view_t& src, const b2i_view_t& dst, int sms, bool last) {
+  if (seg.phases.size() != 2 || env_int("B200IMG_NO_SWEEP", 0) || (L.flags & B2I_LAUNCH_NO_TMA) ||
+      env_int("B200IMG_NO_TMA", 0))
+    return 0;
+  const PhaseDesc& g = seg.phases[0];
+  const PhaseDesc& st = seg.phases[1];
+  if ((g.type != PH_GRAY_REF && g.type != PH_GRAY_CV) || st.type != PH_STENCIL || st.ksize != 3 ||
+      st.cin != 1 || seg.cin != 3)
+    return 0;
+  if ((L.push_rows && (L.push_up.ptr || L.push_dn.ptr)) || L.wait_up_flag || L.wait_dn_flag ||
+      L.signal_up_flag || L.signal_dn_flag)
+    return 0;
+  const bool finish = last && (L.done_flag || L.wait_done_mask);
+  if (finish && !(L.counters && L.status)) return 0;
+  if ((L.W & 7) || L.W < 16 || y1 - y0 < 1) return 0;
+  SweepParams P;
+  memset(&P, 0, sizeof P);
+  P.W = L.W;
+  P.H = L.H;
+  P.y0 = y0;
+  P.y1 = y1;
+  P.src_y_begin = src.y_begin;
+  P.gray = g.type == PH_GRAY_REF ? 1 : 2;
+  P.rgb_order = plan->chain.order == B2I_ORDER_RGB;
+  P.has_lut0 = g.lut >= 0;
+  P.has_lut1 = st.lut >= 0;
+  if (g.lut >= 0) memcpy(P.lut0, seg.luts[g.lut], 256);
+  if (st.lut >= 0) memcpy(P.lut1, seg.luts[st.lut], 256);
+  if (g.lut >= 0 && seg.lut0_affine && !env_int("B200IMG_NO_AFFINE_LUT", 0)) {
+    P.has_lut0 = 2;
+    P.lut0_a = seg.aff_a;
+    P.lut0_b = seg.aff_b;
+    P.lut0_s = seg.aff_s;
+  }
+  P.border = st.border;
+  P.shift = st.shift;
+  P.bias = st.bias;
+  P.expand = st.expand;
+  for (int k = 0; k < 3; ++k) P.wpk[k] = st.wpk[k][0];
+  const int out_row = st.expand ? kSweepOutBytes : kSweepStrip;
+  P.in_stage_bytes = align_up(kSweepChunk * kSweepInBytes, 128);
+  P.out_buf_bytes = align_up(kSweepChunk * out_row, 128);
+  P.warp_smem = kSweepStages * P.in_stage_bytes + 2 * P.out_buf_bytes + 128;  // + dummy slot for the halo lanes
+  CUtensorMap src_map, dst_map;
+  const int src_rows = std::min(src.y_end, L.H) - src.y_begin;
+  if (!encode_map(&src_map, src.ptr, src.pitch, (int64_t)L.W * 3, src_rows, kSweepInBytes, kSweepChunk)) return 0;
+  const uint64_t dptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
+  const bool plain = last && (L.flags & B2I_LAUNCH_DST_MCAST);
+  if (plain) {  // NVLS multicast image: 16-byte stores from the staging buffer, no tensor map on that address
+    if (((dptr | (uint64_t)dst.pitch) & 15) || (((int64_t)L.W * seg.cout) & 15)) return 0;
+    memset(&dst_map, 0, sizeof dst_map);
+    P.plain_dst_ptr = dptr;
+    P.plain_dst_pitch = dst.pitch;
+  } else if (!encode_map(&dst_map, dptr, dst.pitch, (int64_t)L.W * seg.cout, y1 - y0, out_row, kSweepChunk)) {
+    return 0;
+  }
+  // segment height: a multiple of the box height, chosen so that the tasks fill the resident
+  // warps evenly and the two halo rows per segment stay cheap
+  P.n_strips = (L.W + kSweepStrip - 1) / kSweepStrip;
+  const int resident = sms * kSweepCtasPerSm * kSweepWarps;
+  P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kSweepChunk, 6, 96, 2);
+  P.n_tasks = P.n_strips * ((y1 - y0 + P.seg_rows - 1) / P.seg_rows);
+  const int grid = std::max(1, std::min((P.n_tasks + kSweepWarps - 1) / kSweepWarps, sms * kSweepCtasPerSm));
+  plan->info.last_tile_h = -P.seg_rows;  // negative: rows per sweep segment
+  plan->info.last_smem_bytes = P.warp_smem * kSweepWarps;
+  plan->info.last_grid = grid;
+  plan->info.last_blocks_per_sm = kSweepCtasPerSm;
+  plan->info.last_tma_load = plan->info.last_tma_store = 1;
+  plan->info.last_launches++;
+  if (finish) sweep_finish_fill(P, L);
+  cudaError_t e = launch_sweep3(P, src_map, dst_map, grid, (cudaStream_t)L.stream);
+  if (e != cudaSuccess) {
+    b2i::fail(B2I_ERR_CUDA, __FILE__, __LINE__, "sweep3 launch: %s", cudaGetErrorString(e));
+    return -1;
+  }
+  return 1;
+}
+
+// Multi-GPU hooks of the sweep kernels (sweep5.cu, sweep_sobel.cu), with the tile kernel's meaning:
+// waits guard the first segment's ghost-row reads, halo pushes and signals ride on the last
+// segment's result rows. Returns false if the launch asks for something the sweeps do not do (the
+// tile kernel then runs it, or reports the error).
+static bool sweep_hooks_ok(const b2i_launch_t& L, int y0, int y1, bool first, bool last, bool* pushes, bool* flags) {
+  *pushes = last && L.push_rows > 0 && (L.push_up.ptr || L.push_dn.ptr);
+  *flags = (first && (L.wait_up_flag || L.wait_dn_flag)) || (last && (L.signal_up_flag || L.signal_dn_flag));
+  if (*pushes) {
+    if (L.push_rows > y1 - y0 || L.push_rows > kGhostRows) return false;
+    if (L.push_up.ptr && L.push_dn.ptr && L.push_up.pitch != L.push_dn.pitch) return false;
+    const b2i_view_t& v = L.push_up.ptr ? L.push_up : L.push_dn;
+    if ((v.pitch & 7) || ((L.push_up.ptr | L.push_dn.ptr) & 7)) return false;
+    if (L.push_up.ptr && (L.push_up.y_begin > y0 || L.push_up.y_end < y0 + L.push_rows)) return false;
+    if (L.push_dn.ptr && (L.push_dn.y_begin > y1 - L.push_rows || L.push_dn.y_end < y1)) return false;
+  }
+  if ((*flags || (last && (L.done_flag || L.wait_done_mask))) && !(L.counters && L.status)) return false;
+  return true;
+}
+
+
+template <class Params>
+static void sweep_hooks_fill(Params& P, const b2i_launch_t& L, int y0, int y1, bool first, bool last, bool pushes) {
+  P.push_rows = last ? L.push_rows : 0;
+  if (pushes) {
+    P.push_pitch = (int32_t)(L.push_up.ptr ? L.push_up.pitch : L.push_dn.pitch);
+    if (L.push_up.ptr)
+      P.push_up_ptr = L.push_up.ptr + (uint64_t)((int64_t)(y0 - L.push_up.y_begin) * L.push_up.pitch);
+    if (L.push_dn.ptr)
+      P.push_dn_ptr = L.push_dn.ptr + (uint64_t)((int64_t)(y1 - L.push_rows - L.push_dn.y_begin) * L.push_dn.pitch);
+  }
+  if (first) {
+    P.wait_up_flag = L.wait_up_flag;
+    P.wait_dn_flag = L.wait_dn_flag;
+    P.wait_epoch = L.wait_epoch;
+  }
+  if (last) {
+    P.signal_up_flag = L.signal_up_flag;
+    P.signal_dn_flag = L.signal_dn_flag;
+    P.signal_epoch = L.signal_epoch;
+  }
+  // segments whose rows reach into the first / last push_rows rows of the band (exact: the last
+  // of these tasks releases the neighbour's flag)
+  P.n_up_tasks = P.n_strips * ((P.push_rows + P.seg_rows - 1) / P.seg_rows);
+  P.n_dn_tasks = P.n_strips * (P.n_segs - (y1 - y0 - P.push_rows) / P.seg_rows);
+  P.counters = L.counters;
+  P.status = L.status;
+  P.timeout_ns = L.timeout_ns ? L.timeout_ns : 2000000000ull;
+}
+
+// Rows per sweep segment: a multiple of the box height that maximises rows per warp-time. A task
+// costs its rows, the halo rows it reads again, and a fixed part (first TMA round trip, pipeline
+// fill, store drain: about six rows' worth, measured on small bands with scripts/resident_probe.py).
+// Big images end up with one or two waves of tall segments; small bands (a resident pass at N = 8
+// is 540 rows per GPU) with short ones, where the run time is one task's latency.
+static int sweep_seg_rows(int n_strips, int rows, int resident, int chunk, int lo, int hi, int halo_rows) {
+  double best = -1;
+  int pick = lo;
+  for (int sr = lo; sr <= hi; sr += chunk) {
+    const long long tasks = (long long)n_strips * ((rows + sr - 1) / sr);
+    const long long waves = (tasks + resident - 1) / resident;
+    const double eff = (double)tasks / (double)(waves * resident) * sr / (sr + (double)halo_rows + 6.0);
+    if (eff > best + 1e-9) {
+      best = eff;
+      pick = sr;
+    }
+  }
+  return pick;
+}
+
+// The separable sweep kernel (kernels/sweep5.cu) takes segments that are exactly one separable
+// stencil on 3-channel data (+LUT): the 5x5 / 3x3 Gaussians. Returns 1 if it launched, 0 if the
+// segment or the buffers do not qualify, -1 on a launch error.
+int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
+               const b2i_view_t& src, const b2i_view_t& dst, int sms, bool first, bool last) {
+  if (seg.phases.size() != 2 || env_int("B200IMG_NO_SWEEP", 0) || env_int("B200IMG_NO_SWEEP5", 0) ||
+      (L.flags & B2I_LAUNCH_NO_TMA) || env_int("B200IMG_NO_TMA", 0))
+    return 0;
+  const PhaseDesc& ph = seg.phases[0];
+  const PhaseDesc& pv = seg.phases[1];
+  if (ph.type != PH_SEPH || pv.type != PH_SEPV || seg.cin != 3 || seg.cout != 3 || pv.expand) return 0;
+  if ((L.W & 7) || L.W < 16 || L.H < 8 || y1 - y0 < 1) return 0;
+  bool pushes = false, flags = false;
+  if (!sweep_hooks_ok(L, y0, y1, first, last, &pushes, &flags)) return 0;
+  Sweep5Params P;
+  memset(&P, 0, sizeof P);
+  P.W = L.W;
+  P.H = L.H;
+  P.y0 = y0;
+  P.y1 = y1;
+  P.src_y_begin = src.y_begin;
+  P.border = ph.border;
+  // the kernel narrows with a fixed >> 8: scale the vertical taps (and the bias) so that all taps
+  // sum to 256; lanes stay below 65536 (255 * 256 + bias)
+  const int up = 8 - pv.shift;
+  if (up < 0) return 0;
+  P.bias = pv.bias << up;
+  P.has_lut1 = pv.lut >= 0;
+  if (pv.lut >= 0) memcpy(P.lut1, seg.luts[pv.lut], 256);
+  const int off = ph.ksize == 5 ? 0 : 1;  // a 3-tap kernel sits in the middle of the five slots
+  for (int i = 0; i < ph.ksize; ++i) {
+    P.wh[i + off] = ph.sep[i];
+    P.wv[i + off] = pv.sep[i] << up;
+  }
+  static const int b5[5] = {1, 4, 6, 4, 1}, b3[5] = {0, 1, 2, 1, 0};
+  P.binom = !memcmp(P.wh, b5, sizeof b5) || !memcmp(P.wh, b3, sizeof b3);
+  P.in_stage_bytes = align_up(kS5Chunk * kS5InBytes, 128);
+  P.out_buf_bytes = align_up(kS5Chunk * kS5OutBytes, 128);
+  P.warp_smem = kS5Stages * P.in_stage_bytes + 2 * P.out_buf_bytes + 128;
+  CUtensorMap src_map, dst_map;
+  const int src_rows = std::min(src.y_end, L.H) - src.y_begin;
+  if (!encode_map(&src_map, src.ptr, src.pitch, (int64_t)L.W * 3, src_rows, kS5InBytes, kS5Chunk)) return 0;
+  const uint64_t dptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
+  const bool plain = last && (L.flags & B2I_LAUNCH_DST_MCAST);
+  if (plain) {  // NVLS multicast image: 16-byte stores from the staging buffer, no tensor map on that address
+    if (((dptr | (uint64_t)dst.pitch) & 15) || (((int64_t)L.W * seg.cout) & 15)) return 0;
+    memset(&dst_map, 0, sizeof dst_map);
+    P.plain_dst_ptr = dptr;
+    P.plain_dst_pitch = dst.pitch;
+  } else if (!encode_map(&dst_map, dptr, dst.pitch, (int64_t)L.W * 3, y1 - y0, kS5OutBytes, kS5Chunk)) {
+    return 0;
+  }
+  P.n_strips = (L.W + kS5Strip - 1) / kS5Strip;
+  const int resident = sms * kS5CtasPerSm * kS5Warps;
+  P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kS5Chunk, 5, 120, 4);
+  P.n_segs = (y1 - y0 + P.seg_rows - 1) / P.seg_rows;
+  P.n_tasks = P.n_strips * P.n_segs;
+  if (pushes || flags) sweep_hooks_fill(P, L, y0, y1, first, last, pushes);
+  const int grid = std::max(1, std::min((P.n_tasks + kS5Warps - 1) / kS5Warps, sms * kS5CtasPerSm));
+  plan->info.last_tile_h = -P.seg_rows;
+  plan->info.last_smem_bytes = P.warp_smem * kS5Warps;
+  plan->info.last_grid = grid;
+  plan->info.last_blocks_per_sm = kS5CtasPerSm;
+  plan->info.last_tma_load = plan->info.last_tma_store = 1;
+  plan->info.last_launches++;
+  if (last && (L.done_flag || L.wait_done_mask)) sweep_finish_fill(P, L);
+  cudaError_t e = launch_sweep5(P, src_map, dst_map, grid, (cudaStream_t)L.stream);
+  if (e != cudaSuccess) {
+    b2i::fail(B2I_ERR_CUDA, __FILE__, __LINE__, "sweep5 launch: %s", cudaGetErrorString(e));
+    return -1;
+  }
+  return 1;
+}
+
+// The Sobel sweep kernel (kernels/sweep_sobel.cu) takes segments that are exactly one Sobel
+// magnitude on 3-channel data (+LUT). Same return values as try_sweep5.
+int try_sweep_sobel(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
+                    const b2i_view_t& src, const b2i_view_t& dst, int sms, bool first, bool last) {
+  if (seg.phases.size() != 1 || env_int("B200IMG_NO_SWEEP", 0) || env_int("B200IMG_NO_SWEEP_SOBEL", 0) ||
+      (L.flags & B2I_LAUNCH_NO_TMA) || env_int("B200IMG_NO_TMA", 0))
+    return 0;
+  const PhaseDesc& ph = seg.phases[0];
+  if (ph.type != PH_SOBEL || seg.cin != 3 || seg.cout != 3 || ph.expand || ph.border == B2I_BORDER_REF) return 0;
+  if ((L.W & 7) || L.W < 16 || L.H < 8 || y1 - y0 < 1) return 0;
+  bool pushes = false, flags = false;
+  if (!sweep_hooks_ok(L, y0, y1, first, last, &pushes, &flags)) return 0;
+  SweepSobelParams P;
+  memset(&P, 0, sizeof P);
+  P.W = L.W;
+  P.H = L.H;
+  P.y0 = y0;
+  P.y1 = y1;
+  P.src_y_begin = src.y_begin;
+  P.border = ph.border;
+  P.has_lut1 = ph.lut >= 0;
+  if (ph.lut >= 0) memcpy(P.lut1, seg.luts[ph.lut], 256);
+  P.in_stage_bytes = align_up(kSSChunk * kSSInBytes, 128);
+  P.out_buf_bytes = align_up(kSSChunk * kSSOutBytes, 128);
+  P.warp_smem = kSSStages * P.in_stage_bytes + 2 * P.out_buf_bytes + 128;
+  CUtensorMap src_map, dst_map;
+  const int src_rows = std::min(src.y_end, L.H) - src.y_begin;
+  if (!encode_map(&src_map, src.ptr, src.pitch, (int64_t)L.W * 3, src_rows, kSSInBytes, kSSChunk)) return 0;
+  const uint64_t dptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
+  const bool plain = last && (L.flags & B2I_LAUNCH_DST_MCAST);
+  if (plain) {  // NVLS multicast image: 16-byte stores from the staging buffer, no tensor map on that address
+    if (((dptr | (uint64_t)dst.pitch) & 15) || (((int64_t)L.W * seg.cout) & 15)) return 0;
+    memset(&dst_map, 0, sizeof dst_map);
+    P.plain_dst_ptr = dptr;
+    P.plain_dst_pitch = dst.pitch;
+  } else if (!encode_map(&dst_map, dptr, dst.pitch, (int64_t)L.W * 3, y1 - y0, kSSOutBytes, kSSChunk)) {
+    return 0;
+  }
+  P.n_strips = (L.W + kSSStrip - 1) / kSSStrip;
+  const int resident = sms * kSSCtasPerSm * kSSWarps;
+  P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kSSChunk, 4, 120, 2);
+  P.n_segs = (y1 - y0 + P.seg_rows - 1) / P.seg_rows;
+  P.n_tasks = P.n_strips * P.n_segs;
+  if (pushes || flags) sweep_hooks_fill(P, L, y0, y1, first, last, pushes);
+  const int grid = std::max(1, std::min((P.n_tasks + kSSWarps - 1) / kSSWarps, sms * kSSCtasPerSm));
+  plan->info.last_tile_h = -P.seg_rows;
+  plan->info.last_smem_bytes = P.warp_smem * kSSWarps;
+  plan->info.last_grid = grid;
+  plan->info.last_blocks_per_sm = kSSCtasPerSm;
+  plan->info.last_tma_load = plan->info.last_tma_store = 1;
+  plan->info.last_launches++;
+  if (last && (L.done_flag || L.wait_done_mask)) sweep_finish_fill(P, L);
+  cudaError_t e = launch_sweep_sobel(P, src_map, dst_map, grid, (cudaStream_t)L.stream);
+  if (e != cudaSuccess) {
+    b2i::fail(B2I_ERR_CUDA, __FILE__, __LINE__, "sweep_sobel launch: %s", cudaGetErrorString(e));
+    return -1;
+  }
+  return 1;
+}
+
+}  // namespace b2i
