@@ -198,6 +198,9 @@ typedef struct b2i_launch {
   uint32_t wait_done_mask, reserved0;
 } b2i_launch_t;
 
+/* A plan may keep two cuts of its chain: n_segments and seg_* describe the one with
+ * more launches, which is what callers size tmp images by. last_tile_h > 0: tile height of the
+ * tile-chain kernel; < 0: minus the rows per segment of a sweep kernel; 0: streaming pointwise. */
 typedef struct b2i_plan_info {
   int32_t cin, cout, halo, n_segments;
   int32_t seg_pointwise[B2I_MAX_OPS], seg_halo[B2I_MAX_OPS], seg_phases[B2I_MAX_OPS];
