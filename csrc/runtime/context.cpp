@@ -28,6 +28,7 @@
 #include <vector>
 
 #include "../core/error.hpp"
+#include "../core/trace.hpp"
 #include "../kernels/tile_plan.hpp"
 
 #define B2I_CUDA(expr)                                                                  \
@@ -360,6 +361,7 @@ int ensure_tmp(b2i_ctx* c, Dev& d, int n_segments, int rows) {
 // kernel_ms = the slowest GPU's device-event time per iteration (max over "ranks").
 extern "C" int b2i_ctx_run_root(b2i_ctx* c, b2i_plan_t* plan, int iters, int flags, double* kernel_ms,
                                 double* per_gpu_ms /* n entries or null */) {
+  b2i::NvtxRange range("b2i_ctx_run_root");
   B2I_CHECK_ARG(c && plan && c->root_src, "load an image first");
   if (iters < 1) iters = 1;
   b2i_plan_info_t info;
@@ -425,6 +427,7 @@ extern "C" int b2i_ctx_run_root(b2i_ctx* c, b2i_plan_t* plan, int iters, int fla
 // instead of cross-device stream events for the pass-to-pass ordering.
 extern "C" int b2i_ctx_run_resident(b2i_ctx* c, b2i_plan_t* plan, int passes, int flags, int use_flags,
                                     double* kernel_ms, double* per_gpu_ms) {
+  b2i::NvtxRange range("b2i_ctx_run_resident");
   B2I_CHECK_ARG(c && plan && c->root_src, "load an image first");
   if (passes < 1) passes = 1;
   for (int i = 0; i < c->n; ++i)  // bands sharing one physical GPU must not spin on each other
@@ -601,6 +604,7 @@ extern "C" int b2i_ctx_run_resident(b2i_ctx* c, b2i_plan_t* plan, int passes, in
 extern "C" int b2i_ctx_run_direct(b2i_ctx* c, b2i_plan_t* plan, const uint8_t* src, int W, int H, int C,
                                   size_t src_pitch, uint8_t* dst, size_t dst_pitch, int flags,
                                   double* total_ms) {
+  b2i::NvtxRange range("b2i_ctx_run_direct");
   B2I_CHECK_ARG(c && plan && src && dst, "bad arguments");
   b2i_plan_info_t info;
   B2I_TRY(b2i_plan_info(plan, &info));

@@ -13,6 +13,7 @@
 #include <cstdlib>
 #include <cstring>
 
+#include "../core/trace.hpp"
 #include "plan_internal.hpp"
 
 using namespace b2i;
@@ -451,6 +452,7 @@ extern "C" int b2i_cuda_run(b2i_plan_t* plan, const b2i_launch_t* Lp) {
   B2I_CHECK_ARG(L.W > 0 && L.H > 0 && 0 <= L.y0 && L.y0 <= L.y1 && L.y1 <= L.H,
                 "bad geometry %dx%d rows [%d,%d)", L.W, L.H, L.y0, L.y1);
   if (L.y0 == L.y1) return B2I_OK;
+  NvtxRange range("b2i_cuda_run");
   plan->info.last_launches = 0;
   // the split cut only where the sweep kernels can take it: 8-pixel widths, TMA-encodable views
   // and tmp images; anything else runs the fused cut on the tile kernel
