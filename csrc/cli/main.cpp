@@ -291,11 +291,26 @@ int main(int argc, char** argv) {
   b2i_chain_describe(&chain, desc, sizeof desc);
   const double mp = (double)W * H / 1e6;
   if (o.json) {
+    // GPU runs also say what the filter had to move and how close to the memory roofline it ran:
+    // every input and output byte crosses HBM once (B200IMG_HBM_GBS overrides the measured
+    // 6545 GB/s copy bandwidth); in ROOT mode with equal bands the other GPUs' share of those bytes
+    // crosses the root GPU's NVLink port as well.
+    char roof[256] = "";
+    if ((backend == "cuda" || backend == "naive") && kernel_ms > 0) {
+      const char* env = getenv("B200IMG_HBM_GBS");
+      const double hbm_gbs = env && atof(env) > 0 ? atof(env) : 6545.0;
+      const double bytes = (double)W * H * (C + out_c);  // filter_ms is per pass / per iteration
+      const double roof_ms = bytes / (hbm_gbs * 1e6);
+      const int gpus = n > 1 ? n : 1;
+      const double link_bytes = (gpus > 1 && !o.resident) ? bytes * (gpus - 1) / gpus : 0.0;
+      snprintf(roof, sizeof roof, ", \"hbm_bytes\": %.0f, \"hbm_roofline_ms\": %.6f, \"of_hbm_roofline\": %.3f, "
+               "\"nvlink_bytes_equal_bands\": %.0f", bytes, roof_ms / gpus, roof_ms / gpus / kernel_ms, link_bytes);
+    }
     printf("{\"input\": \"%s\", \"W\": %d, \"H\": %d, \"C\": %d, \"chain\": \"%s\", \"backend\": \"%s\", "
            "\"workers\": %d, \"filter_ms\": %.6f, \"total_ms\": %.3f, \"mpix_per_s\": %.1f, "
-           "\"output\": \"%s\"%s%s}\n",
+           "\"output\": \"%s\"%s%s%s}\n",
            source.c_str(), W, H, C, desc, backend.c_str(), n, kernel_ms, total_ms,
-           kernel_ms > 0 ? mp / (kernel_ms / 1e3) : 0.0, outp.c_str(), report[0] ? ", \"runtime\": " : "",
+           kernel_ms > 0 ? mp / (kernel_ms / 1e3) : 0.0, outp.c_str(), roof, report[0] ? ", \"runtime\": " : "",
            report[0] ? report.data() : "");
   } else {
     printf("Image properties: W=%d   H=%d   C=%d  (%s)\n", W, H, C, source.c_str());

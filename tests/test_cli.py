@@ -84,7 +84,9 @@ def test_cuda_backend_single_and_multi_band(tmp_path):
     r = subprocess.run([_exe(), "--input", "in.ppm", "--output", "o2.ppm", "--backend", "cuda", "-np", "2",
                         "--replicate", "--json"], cwd=tmp_path, capture_output=True, text=True)
     assert r.returncode == 0, r.stderr + r.stdout
-    rep = json.loads(r.stdout)["runtime"]
+    line = json.loads(r.stdout)
+    assert line["hbm_roofline_ms"] > 0 and 0 < line["of_hbm_roofline"] < 1.5 and line["nvlink_bytes_equal_bands"] > 0
+    rep = line["runtime"]
     assert rep["mode"].startswith("root/replicated") and rep["replicas_identical"] == "yes", rep
     assert np.array_equal(b2.read_image(str(tmp_path / "o2.ppm")), want)
     r = subprocess.run([_exe(), "--topology"], capture_output=True, text=True)
