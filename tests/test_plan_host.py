@@ -47,3 +47,45 @@ def test_long_chains_split_by_phase_and_halo_budget():
 def test_channel_mismatch_is_an_error():
     with pytest.raises(b2.B200ImgError):
         Plan("expand", 3)
+
+
+def _plan_debug(chains):
+    import os
+    import subprocess
+    import sys
+    env = dict(os.environ, B200IMG_DEBUG="2")
+    code = ("import sys\nfrom mpi_cuda_imagemanipulation_b200.ops.cuda import Plan\n"
+            f"for c in {list(chains)!r}:\n    print('chain', c, file=sys.stderr, flush=True); Plan(c, 3)\n")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env,
+                       cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0, r.stderr
+    out, cur = {}, None
+    for line in r.stderr.splitlines():
+        if line.startswith("chain "):
+            cur = line[6:]
+            out[cur] = ""
+        elif cur is not None:
+            out[cur] += line + "\n"
+    return out
+
+
+def test_contrast_tables_are_recognised_as_affine():
+    """The sweep kernel computes clamp((a v + b) >> s) tables instead of looking them up; the planner
+    finds (a, b, s) by exhaustive check (kernel.cu:56 with 3.5, kern.cpp:74)."""
+    d = _plan_debug(["kernel_cu", "kern_cpp", "gray,invert,emboss3,expand", "gray,contrast:2.2,emboss3,expand"])
+    assert "is clamp((7 v + -640) >> 1)" in d["kernel_cu"]
+    assert "is clamp((3 v + -256) >> 0)" in d["kern_cpp"]
+    assert "is clamp((-1 v + 255) >> 0)" in d["gray,invert,emboss3,expand"]
+    assert "is not clamp" in d["gray,contrast:2.2,emboss3,expand"]
+
+
+def test_library_path_override():
+    import os
+    import subprocess
+    import sys
+    from mpi_cuda_imagemanipulation_b200 import _lib
+    env = dict(os.environ, B200IMG_LIB=_lib.LIB_PATH)
+    r = subprocess.run([sys.executable, "-c", "import mpi_cuda_imagemanipulation_b200._lib as l; print(l.LIB_PATH)"],
+                       capture_output=True, text=True, env=env,
+                       cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0 and r.stdout.strip() == _lib.LIB_PATH, r.stderr
