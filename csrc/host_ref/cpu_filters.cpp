@@ -83,6 +83,35 @@ static inline uint8_t stencil_at(const b2i_op_t& op, const RowWindow& in, int H,
   return clamp_u8((s + op.bias) >> op.shift);
 }
 
+// Pixels [x0, x1] of one row where every tap is inside the image: no coordinate mapping.
+template <int K, bool SOBEL>
+static void interior_run(const b2i_op_t& op, const uint8_t* const (&rows)[5], uint8_t* o, int x0, int x1, int C) {
+  constexpr int r = K / 2;
+  int w[K * K];
+  for (int q = 0; q < K * K; ++q) w[q] = SOBEL ? 0 : op.weights[q];
+  const size_t n = (size_t)(x1 - x0 + 1) * C;  // channel values are independent: one flat loop
+  const size_t first = (size_t)(x0 - r) * C;
+  uint8_t* out = o + (size_t)x0 * C;
+  for (size_t e = 0; e < n; ++e) {
+    const size_t base = first + e;
+    if (SOBEL) {
+      int gx = 0, gy = 0;
+      for (int j = 0; j < 3; ++j)
+        for (int i = 0; i < 3; ++i) {
+          const int v = rows[j][base + (size_t)i * C];
+          gx += kSobelX[j * 3 + i] * v;
+          gy += kSobelY[j * 3 + i] * v;
+        }
+      out[e] = clamp_u8(std::abs(gx) + std::abs(gy));
+    } else {
+      int s = 0;
+      for (int j = 0; j < K; ++j)
+        for (int i = 0; i < K; ++i) s += w[j * K + i] * rows[j][base + (size_t)i * C];
+      out[e] = clamp_u8((s + op.bias) >> op.shift);
+    }
+  }
+}
+
 // Rows [out.ya, out.yb) of `op` applied to the whole H-row image; `in` must hold every source
 // row the border rule can touch for those rows.
 static void apply_stencil(const b2i_op_t& op, const RowWindow& in, int H, RowWindow& out) {
@@ -109,35 +138,31 @@ static void apply_stencil(const b2i_op_t& op, const RowWindow& in, int H, RowWin
     for (int x = cx0; x <= cx1; ++x) {
       if (y_interior && x >= ix0 && x <= ix1) {
         // fast path for the run [x, ix1]
-        const uint8_t* rows[5];
+        const uint8_t* rows[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
         for (int j = 0; j < k; ++j) rows[j] = in.row(y + j - r);
-        for (; x <= ix1; ++x) {
-          for (int c = 0; c < C; ++c) {
-            const size_t base = (size_t)(x - r) * C + c;
-            if (op.kind == B2I_OP_SOBEL) {
-              int gx = 0, gy = 0;
-              for (int j = 0; j < 3; ++j)
-                for (int i = 0; i < 3; ++i) {
-                  const int v = rows[j][base + (size_t)i * C];
-                  gx += kSobelX[j * 3 + i] * v;
-                  gy += kSobelY[j * 3 + i] * v;
-                }
-              o[(size_t)x * C + c] = clamp_u8(std::abs(gx) + std::abs(gy));
-            } else {
-              int s = 0;
-              for (int j = 0; j < k; ++j)
-                for (int i = 0; i < k; ++i) s += op.weights[j * k + i] * rows[j][base + (size_t)i * C];
-              o[(size_t)x * C + c] = clamp_u8((s + op.bias) >> op.shift);
-            }
-          }
-        }
-        --x;  // the outer loop increments
+        // the same sums as stencil_at, with the kernel size known to the compiler
+        if (op.kind == B2I_OP_SOBEL) interior_run<3, true>(op, rows, o, x, ix1, C);
+        else if (k == 3) interior_run<3, false>(op, rows, o, x, ix1, C);
+        else interior_run<5, false>(op, rows, o, x, ix1, C);
+        x = ix1;  // the outer loop increments
         continue;
       }
       for (int c = 0; c < C; ++c) o[(size_t)x * C + c] = stencil_at(op, in, H, x, y, c);
     }
   }
 }
+
+// v*11/100, v*59/100, v*3/10 with the reference's per-term integer truncation (kernel.cu:39-42).
+struct GrayRefTables {
+  uint8_t b[256], g[256], r[256];
+  GrayRefTables() {
+    for (int v = 0; v < 256; ++v) {
+      b[v] = (uint8_t)(v * 11 / 100);
+      g[v] = (uint8_t)(v * 59 / 100);
+      r[v] = (uint8_t)(v * 3 / 10);
+    }
+  }
+};
 
 static void apply_pointwise(const b2i_op_t& op, int order, const RowWindow& in, RowWindow& out) {
   const int W = in.W;
@@ -147,8 +172,10 @@ static void apply_pointwise(const b2i_op_t& op, int order, const RowWindow& in, 
     switch (op.kind) {
       case B2I_OP_GRAY_REF: {
         const int ib = order == B2I_ORDER_BGR ? 0 : 2, ir = 2 - ib;
+        // kernel.cu:39-42 term by term; the three truncated products come from 256-entry tables
+        static const GrayRefTables t;
         for (int x = 0; x < W; ++x)
-          o[x] = (uint8_t)(s[3 * x + ib] * 11 / 100 + s[3 * x + 1] * 59 / 100 + s[3 * x + ir] * 3 / 10);
+          o[x] = (uint8_t)(t.b[s[3 * x + ib]] + t.g[s[3 * x + 1]] + t.r[s[3 * x + ir]]);
         break;
       }
       case B2I_OP_GRAY_CV: {
