@@ -33,7 +33,7 @@ struct State {
   unsigned char* data = nullptr;
   size_t data_bytes = 0;
   int local_sense = 0;
-  long long t_scatter_ns = 0, t_gather_ns = 0;
+  long long t_scatter_ns = 0, t_scatter_exit_ns = 0, t_gather_ns = 0;
 };
 inline State& st() {
   static State s;
@@ -56,7 +56,32 @@ inline void barrier() {
   }
 }
 inline size_t type_size(MPI_Datatype t) { return t == MPI_INT ? 4 : 1; }
+
+#ifdef __CUDACC__
+// Harness-side clocks around CUDA context creation, so that the reference's driver start-up
+// (cudaSetDevice after MPI_Scatter, kernel.cu:137,147) can be reported apart from its work.
+// B2I_REF_PREWARM=1 creates the context inside MPI_Init instead, i.e. before the scatter ->
+// gather window opens; the reference source itself is untouched either way.
+inline cudaError_t timed_set_device(int dev) {
+  const long long t0 = now_ns();
+  cudaError_t e = cudaSetDevice(dev);
+  if (e == cudaSuccess) e = cudaFree(0);
+  fprintf(stderr, "[shim cuda] rank=%d ctx_init_ns=%lld where=cudaSetDevice\n", st().rank, now_ns() - t0);
+  return e;
+}
+inline void prewarm_context() {
+  const char* p = getenv("B2I_REF_PREWARM");
+  if (!p || p[0] != '1') return;
+  const long long t0 = now_ns();
+  cudaSetDevice(0);  // the device the reference picks on every rank (kernel.cu:147)
+  cudaFree(0);
+  fprintf(stderr, "[shim cuda] rank=%d ctx_init_ns=%lld where=MPI_Init\n", st().rank, now_ns() - t0);
+}
+#endif
 }  // namespace b2i_shim_mpi
+#ifdef __CUDACC__
+#define cudaSetDevice(dev) b2i_shim_mpi::timed_set_device(dev)
+#endif
 
 inline int MPI_Init(int*, char***) {
   using namespace b2i_shim_mpi;
@@ -91,6 +116,9 @@ inline int MPI_Init(int*, char***) {
     s.hdr = &local;
     s.data = (unsigned char*)malloc(s.data_bytes);
   }
+#ifdef __CUDACC__
+  prewarm_context();
+#endif
   return MPI_SUCCESS;
 }
 inline int MPI_Comm_rank(MPI_Comm, int* rank) {
@@ -129,6 +157,7 @@ inline int MPI_Scatter(const void* send, int sendcount, MPI_Datatype st_, void* 
   barrier();
   memcpy(recv, s.data + n * s.rank, (size_t)recvcount * type_size(rt));
   barrier();
+  if (s.rank == root) s.t_scatter_exit_ns = now_ns();
   return MPI_SUCCESS;
 }
 inline int MPI_Gather(const void* send, int sendcount, MPI_Datatype st_, void* recv, int recvcount,
@@ -144,6 +173,9 @@ inline int MPI_Gather(const void* send, int sendcount, MPI_Datatype st_, void* r
     s.t_gather_ns = now_ns();
     // harness-side end-to-end window: entering MPI_Scatter -> leaving MPI_Gather on the root
     fprintf(stderr, "[shim mpi] scatter_to_gather_ns=%lld\n", s.t_gather_ns - s.t_scatter_ns);
+    // leaving MPI_Scatter -> leaving MPI_Gather: kern.cpp's own window (kern.cpp:60,86) in ns
+    // (it prints whole milliseconds only)
+    fprintf(stderr, "[shim mpi] after_scatter_to_gather_ns=%lld\n", s.t_gather_ns - s.t_scatter_exit_ns);
   }
   return MPI_SUCCESS;
 }

@@ -30,11 +30,9 @@ sys.path.insert(0, ROOT)
 # NCCL writes its version banner to stdout by default; stdout carries exactly one JSON line here
 os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
-W8K, H8K = 7680, 4320
+from bench_common import H8K, W8K, config_block  # noqa: E402  (pure Python: loads no native code)
+
 CHAIN = "kernel_cu"
-
-
-from mpi_cuda_imagemanipulation_b200.utils.clocks import ClockSampler  # noqa: E402
 
 
 # ---- our arm ------------------------------------------------------------------------------------
@@ -43,6 +41,7 @@ def run_ours(args) -> dict:
 
     import mpi_cuda_imagemanipulation_b200 as b2
     from mpi_cuda_imagemanipulation_b200.ops.cuda import Plan
+    from mpi_cuda_imagemanipulation_b200.utils.clocks import ClockSampler
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -124,9 +123,9 @@ def run_ours(args) -> dict:
         "value": round(value, 1), "unit": "MP/s", "n_gpus": 1, "steps": K, "warmup": max(Wm, 3),
         "ms_per_step": round(ms, 6), "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "uint8", "data": "synthetic",
-        "config": {"model": "kernel_cu pipeline: gray->contrast3.5->emboss3x3->BGR (kernel.cu:192-210)",
-                   "image": f"{W}x{H} RGB", "global_batch": 1, "seq_len": W * H, "parallelism": "bands1",
-                   "l2": f"inputs rotate over {NB} image pairs ({NB * bytes_step / 1e6:.0f} MB) > 126 MB L2",
+        "config": config_block(W, H, 1),
+        "effective_gpus": 1,
+        "detail": {"l2": f"inputs rotate over {NB} image pairs ({NB * bytes_step / 1e6:.0f} MB) > 126 MB L2",
                    "timed_as": f"{K} steps in one CUDA graph, median of {args.repeats} replays"},
         "clocks": clk.summary(),
         "e2e": {"value": round(mp / (e2e_ms / 1e3), 1), "unit": "MP/s", "ms_per_step": round(e2e_ms, 4),
