@@ -37,6 +37,22 @@ bool encode_map(CUtensorMap* m, uint64_t ptr, int64_t pitch, int64_t row_bytes, 
              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// 2-D byte image as a tensor of bytes with 128-byte-swizzled boxes of 128 bytes x box_rows: the
+// shared-memory layout the tensor cores read K-major operands from (kernels/stencil_mma.cu). Byte
+// elements: any row length clips correctly, only the base and the pitch must be 16-byte aligned.
+bool encode_map_sw128(CUtensorMap* m, uint64_t ptr, int64_t pitch, int64_t row_bytes, int rows, int box_rows) {
+  auto enc = tensor_map_encoder();
+  if (!enc || rows <= 0 || row_bytes <= 0) return false;
+  if ((ptr & 15) || (pitch & 15) || pitch <= 0 || box_rows > 256) return false;
+  cuuint64_t gdim[2] = {(cuuint64_t)row_bytes, (cuuint64_t)rows};
+  cuuint64_t gstr[1] = {(cuuint64_t)pitch};
+  cuuint32_t box[2] = {128u, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, reinterpret_cast<void*>(ptr), gdim, gstr, box, estr,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 int align_up(int v, int a) { return (v + a - 1) / a * a; }
 
 // Shared-memory layout of a tile segment for tile height th. Every buffer starts 128-byte
@@ -94,6 +110,7 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
     B2I_CHECK_ARG(src.y_begin <= need_a && src.y_end >= need_b && dst.y_begin <= y0 && dst.y_end >= y1,
                   "views do not cover the band [%d,%d) and its halo", y0, y1);
     int sw = try_sweep(plan, seg, L, y0, y1, src, dst, sms, last);
+    if (sw == 0) sw = try_stencil_mma(plan, seg, L, y0, y1, src, dst, sms, first, last);
     if (sw == 0) sw = try_sweep5(plan, seg, L, y0, y1, src, dst, sms, first, last);
     if (sw == 0) sw = try_sweep_sobel(plan, seg, L, y0, y1, src, dst, sms, first, last);
     if (sw < 0) return B2I_ERR_CUDA;

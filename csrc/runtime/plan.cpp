@@ -203,6 +203,32 @@ int build_tile_segment(const std::vector<Elem>& el, int cin, Segment& seg) {
   }
   if (seg.phases.empty() || (int)seg.phases.size() > kMaxPhases) return B2I_ERR_UNSUPPORTED;
   seg.cout = c;
+  // exactly one stencil and nothing else: the tensor-core kernel's shape (kernels/stencil_mma.cu)
+  seg.mma_ok = 0;
+  if (el.size() == 1 && (el[0].kind == B2I_OP_STENCIL || el[0].kind == B2I_OP_SOBEL) && cin == c &&
+      el[0].op->border != B2I_BORDER_REF) {
+    const b2i_op_t& op = *el[0].op;
+    memset(seg.mma_w, 0, sizeof seg.mma_w);
+    seg.mma_border = op.border;
+    if (op.kind == B2I_OP_SOBEL) {
+      const int8_t gx[9] = {-1, 0, 1, -2, 0, 2, -1, 0, 1}, gy[9] = {-1, -2, -1, 0, 0, 0, 1, 2, 1};
+      for (int q = 0; q < 9; ++q) {
+        seg.mma_w[0][q / 3][q % 3] = gx[q];
+        seg.mma_w[1][q / 3][q % 3] = gy[q];
+      }
+      seg.mma_mode = SM_SOBEL;
+      seg.mma_R = 1;
+      seg.mma_shift = seg.mma_bias = 0;
+      seg.mma_ok = 1;
+    } else if ((op.ksize == 3 || op.ksize == 5) && op.shift >= 0 && op.shift <= 16) {
+      for (int q = 0; q < op.ksize * op.ksize; ++q) seg.mma_w[0][q / op.ksize][q % op.ksize] = op.weights[q];
+      seg.mma_mode = SM_LINEAR;
+      seg.mma_R = op.ksize / 2;
+      seg.mma_shift = op.shift;
+      seg.mma_bias = op.bias;
+      seg.mma_ok = 1;
+    }
+  }
   // margins, walking backwards: a phase must produce what the later stencils still consume
   int margin = 0, margin_x = 0;
   for (int k = (int)seg.phases.size() - 1; k >= 0; --k) {
@@ -284,11 +310,19 @@ bool build_pointwise_segment(const std::vector<Elem>& el, int cin, Segment& seg)
 
 // A segment the sweep kernels sweep5.cu / sweep_sobel.cu take (given a fitting image).
 bool sweep_shape(const Segment& seg) {
+  if (!seg.pointwise && seg.mma_ok) return true;  // any channel count: the tensor-core kernel works on bytes
   if (seg.pointwise || seg.cin != 3 || seg.cout != 3) return false;
   if (seg.phases.size() == 2)
     return seg.phases[0].type == PH_SEPH && seg.phases[1].type == PH_SEPV && !seg.phases[1].expand;
   return seg.phases.size() == 1 && seg.phases[0].type == PH_SOBEL && !seg.phases[0].expand &&
          seg.phases[0].border != B2I_BORDER_REF;
+}
+
+// gray (+LUT) -> one 3x3 stencil on the gray plane (+LUT, +expand): what sweep3.cu takes (try_sweep).
+bool sweep3_shape(const Segment& seg) {
+  return !seg.pointwise && seg.cin == 3 && seg.phases.size() == 2 &&
+         (seg.phases[0].type == PH_GRAY_REF || seg.phases[0].type == PH_GRAY_CV) &&
+         seg.phases[1].type == PH_STENCIL && seg.phases[1].ksize == 3 && seg.phases[1].cin == 1;
 }
 
 // Is the table clamp((a v + b) >> s) for small integers? Contrast stretches are (kernel.cu:56 with
@@ -361,6 +395,14 @@ int segment_chain(const std::vector<Elem>& el, int in_channels, bool split, std:
       }
       if (!ok) break;
       if (split && have && sweep_shape(best) && !sweep_shape(seg)) break;
+      // a pointwise prefix followed by a stencil the tensor-core kernel takes on its own: two
+      // launches (streaming kernel, then stencil_mma) beat the fused tile kernel -- unless the
+      // fused segment is the reference pipeline's shape, which sweep3.cu runs in one pass
+      if (split && have && best.pointwise && !seg.pointwise && !sweep3_shape(seg)) {
+        Segment alone;
+        std::vector<Elem> one(el.begin() + end - 1, el.begin() + end);
+        if (build_tile_segment(one, best.cout, alone) == B2I_OK && alone.mma_ok) break;
+      }
       best = seg;
       best_end = end;
       have = true;

@@ -11,6 +11,7 @@
 #include "../kernels/sweep3.hpp"
 #include "../kernels/sweep5.hpp"
 #include "../kernels/sweep_sobel.hpp"
+#include "../kernels/stencil_mma.hpp"
 #include "../kernels/tile_plan.hpp"
 
 namespace b2i {
@@ -26,6 +27,8 @@ cudaError_t launch_sweep_sobel(const SweepSobelParams& P, const CUtensorMap& src
                                int grid, cudaStream_t stream);
 cudaError_t launch_sweep3(const SweepParams& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
                           int grid, cudaStream_t stream);
+cudaError_t launch_stencil_mma(const StencilMmaParams& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
+                               int grid, cudaStream_t stream);
 int run_naive(const b2i_chain_t* chain, const uint8_t* src, int W, int H, int C, size_t src_pitch,
               uint8_t* dst, size_t dst_pitch, uint8_t* tmp0, uint8_t* tmp1, uint8_t* lut_scratch,
               cudaStream_t stream);
@@ -43,6 +46,10 @@ struct Segment {
   // the first phase's LUT as clamp((a v + b) >> s), if it is one (found once, at plan creation)
   int lut0_affine = 0;
   int32_t aff_a = 0, aff_b = 0, aff_s = 0;
+  // a segment that is exactly one stencil (or the Sobel pair) with int8 weights and a border rule
+  // other than REF: the tensor-core kernel (kernels/stencil_mma.cu) takes it
+  int mma_ok = 0, mma_mode = 0, mma_R = 0, mma_shift = 0, mma_bias = 0, mma_border = 0;
+  int8_t mma_w[2][5][5];
   // pointwise segments
   int pw_gray = 0, pw_expand = 0, pw_has_lut0 = 0, pw_has_lut1 = 0;
   uint8_t pw_lut0[256], pw_lut1[256];
@@ -55,6 +62,7 @@ int device_sms(int dev, int* sms);
 PFN_cuTensorMapEncodeTiled_v12000 tensor_map_encoder();
 bool encode_map(CUtensorMap* m, uint64_t ptr, int64_t pitch, int64_t row_bytes, int rows, int box_w_bytes,
                 int box_rows);
+bool encode_map_sw128(CUtensorMap* m, uint64_t ptr, int64_t pitch, int64_t row_bytes, int rows, int box_rows);
 void layout(const Segment& seg, int th, TileParams& P, int raw_stages = 2);
 }  // namespace b2i
 
@@ -81,6 +89,8 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
 int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1, const b2i_view_t& src,
                const b2i_view_t& dst, int sms, bool first, bool last);
 int try_sweep_sobel(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
+                    const b2i_view_t& src, const b2i_view_t& dst, int sms, bool first, bool last);
+int try_stencil_mma(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
                     const b2i_view_t& src, const b2i_view_t& dst, int sms, bool first, bool last);
 // set by a sweep launcher that fused ROOT mode's completion flags into its kernel
 extern thread_local bool g_wait_done_fused;

@@ -30,18 +30,28 @@ def test_stencils_the_sweep_kernels_take_stand_alone():
     assert _info("gauss5")["n_segments"] == 1
     assert _info("gauss5,invert")["n_segments"] == 1          # a LUT rides on the stencil's result
     assert _info("gauss5,gauss5,gauss5")["n_segments"] == 3
-    # on one channel there is no sweep kernel: the tile kernel takes the whole chain
-    assert _info("gray,gauss5,sobel,expand")["n_segments"] == 1
-    assert _info("gauss5,sobel", c=1)["n_segments"] == 1
+    # the tensor-core stencil kernel works on bytes, so one-channel stencils stand alone too, and a
+    # pointwise prefix is cut off in front of them (streaming kernel, then stencil_mma)
+    assert _info("gauss5,sobel", c=1)["n_segments"] == 2
+    assert [s["pointwise"] for s in _info("gray,gauss5")["segments"]] == [True, False]
+    assert _info("gray,gauss5,sobel,expand")["n_segments"] == 4
+    # ... but the reference pipeline's shape stays one launch (sweep3.cu)
+    assert _info("kernel_cu")["n_segments"] == 1 and _info("kern_cpp")["n_segments"] == 1
+    # REF borders are not the tensor-core kernel's: emboss5@ref after gray stays fused
+    assert _info("gray,emboss5")["n_segments"] == 1
     # border=ref stencils are not separable sweeps
     assert _info("gauss5@ref,sobel@ref")["n_segments"] == 1
 
 
 def test_long_chains_split_by_phase_and_halo_budget():
     """A tile segment holds at most 6 phases (a separable stencil is two) and a summed radius of 8."""
-    i = _info("gray,gauss5,gauss5,gauss5,gauss5,gauss5,sobel,expand")
-    assert i["n_segments"] == 3 and i["halo"] == 11
+    # stencils with the reference's border rule stay on the tile kernel: its budgets cut the chain
+    i = _info("gray,emboss5,emboss5,emboss5,emboss5,emboss5,sobel@ref,expand")
+    assert i["n_segments"] == 2 and i["halo"] == 11
     assert sum(s["halo"] for s in i["segments"]) == 11 and i["segments"][-1]["cout"] == 3
+    # the same chain of stencils the tensor-core kernel takes is one launch per op
+    i = _info("gray,gauss5,gauss5,gauss5,gauss5,gauss5,sobel,expand")
+    assert i["n_segments"] == 8 and i["halo"] == 11 and sum(s["halo"] for s in i["segments"]) == 11
 
 
 def test_channel_mismatch_is_an_error():
