@@ -18,8 +18,6 @@
 // uses.
 #include <cuda_runtime.h>
 
-#include <mutex>
-
 #include "../core/error.hpp"
 #include "b200img.h"
 
@@ -34,27 +32,19 @@ static_assert(2 * kImageBytes + kTableBytes == B2I_NOALLOC_SCRATCH_BYTES,
 // NOT a device address; the address is looked up per device with cudaGetSymbolAddress below.
 static __device__ __align__(256) unsigned char g_scratch[B2I_NOALLOC_SCRATCH_BYTES];
 
-constexpr int kMaxDevices = 64;
-std::mutex g_mu;
-unsigned char* g_base[kMaxDevices] = {nullptr};
-
-// Device address of g_scratch on the current device; looked up once per device, with that
-// device current, and remembered.
+// Device address of g_scratch on the current device, with that device current. Asked for on every
+// call rather than remembered: the lookup allocates nothing once the module is loaded (the first
+// call per device loads it), and a remembered address would dangle after cudaDeviceReset - which
+// the reference itself calls (kernel.cu:241) - or any other teardown of the primary context.
 int scratch_base(unsigned char** base) {
-  int dev = -1;
-  cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess) B2I_FAIL(B2I_ERR_CUDA, "cudaGetDevice: %s", cudaGetErrorString(e));
-  B2I_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "device ordinal %d is beyond the %d this entry point tracks",
-                dev, kMaxDevices);
-  std::lock_guard<std::mutex> lock(g_mu);
-  if (!g_base[dev]) {
-    void* p = nullptr;
-    e = cudaGetSymbolAddress(&p, g_scratch);
-    if (e != cudaSuccess || !p)
-      B2I_FAIL(B2I_ERR_CUDA, "cudaGetSymbolAddress(scratch) on device %d: %s", dev, cudaGetErrorString(e));
-    g_base[dev] = static_cast<unsigned char*>(p);
+  void* p = nullptr;
+  const cudaError_t e = cudaGetSymbolAddress(&p, g_scratch);
+  if (e != cudaSuccess || !p) {
+    int dev = -1;
+    cudaGetDevice(&dev);
+    B2I_FAIL(B2I_ERR_CUDA, "cudaGetSymbolAddress(scratch) on device %d: %s", dev, cudaGetErrorString(e));
   }
-  *base = g_base[dev];
+  *base = static_cast<unsigned char*>(p);
   return B2I_OK;
 }
 

@@ -29,6 +29,13 @@
 //     elected lane; tcgen05.commit frees slabs and publishes chunks), warps 2-5 are the epilogue.
 //     One CTA per SM, persistent: every CTA takes a contiguous run of slabs.
 //
+// Measured on B200 (8K RGB; scripts/kbench.py, scripts/mma_timeline.py, profiles/mma_notes.md): without
+// the MMAs the kernel moves its 210 MB at 6.5 TB/s (0.77 us per slab and SM); an M = 128 MMA with
+// both operands in shared memory takes ~110 cycles whatever its N (16, 32 and 64 time the same: the
+// 128 operand rows are the cost), so 12 MMAs per slab (3 x 3) hide behind the memory traffic and 20
+// (5 x 5) do not: 3 x 3 stencils 47 us, 5 x 5 stencils 55 us, any weights, any channel count. Staging
+// A through TMEM (tcgen05.cp, then the MMA reads A from TMEM) was tried and is slower (92 us).
+//
 // Exact: u8 x s8 products accumulate in s32. Reference: kernel.cu:64-94 is this correlation with
 // one thread per pixel and seven byte loads per output; kern.cpp:75 is cv::filter2D.
 #include "b200img.h"
@@ -97,26 +104,6 @@ __device__ __forceinline__ void umma_i8_w(uint32_t d_tmem, uint32_t a_lo, uint32
       "setp.ne.b32 p, %6, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::i8 [%0], da, db, %5, {%7, %7, %7, %7}, p;\n\t}"
       ::"r"(d_tmem), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(1u), "r"(0u)
-      : "memory");
-}
-// The A operand through TMEM: tcgen05.cp moves a 128-row x 32-byte K slice (same descriptor as an A
-// operand in shared memory) into 8 TMEM columns, and the MMA reads it from there. cp and mma run in
-// issue order on the tensor pipe, so neither needs a barrier against the other.
-__device__ __forceinline__ void tmem_cp_128x256b(uint32_t taddr, uint32_t s_lo, uint32_t s_hi) {
-  asm volatile(
-      "{\n\t.reg .b64 ds;\n\t"
-      "mov.b64 ds, {%1, %2};\n\t"
-      "tcgen05.cp.cta_group::1.128x256b [%0], ds;\n\t}"
-      ::"r"(taddr), "r"(s_lo), "r"(s_hi)
-      : "memory");
-}
-__device__ __forceinline__ void umma_i8_ts(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t b_hi, uint32_t idesc) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\t"
-      "mov.b64 db, {%2, %3};\n\t"
-      "setp.ne.b32 p, %5, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], db, %4, {%6, %6, %6, %6}, p;\n\t}"
-      ::"r"(d_tmem), "r"(a_tmem), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(1u), "r"(0u)
       : "memory");
 }
 constexpr uint32_t kADescHi = (1024u >> 4) | (1u << 14) | (2u << 29);  // SBO 1024, version 1, 128-byte swizzle
@@ -194,7 +181,7 @@ __device__ __forceinline__ int run_last_slab(const Run& r, int n_slabs) { return
 
 }  // namespace
 
-template <int NDY, int NACC, bool TS>
+template <int NDY, int NACC>
 __global__ void __launch_bounds__(kSmThreads, 1)
 stencil_mma_kernel(const __grid_constant__ StencilMmaParams P, const __grid_constant__ CUtensorMap src_map,
                    const __grid_constant__ CUtensorMap dst_map) {
@@ -208,8 +195,7 @@ stencil_mma_kernel(const __grid_constant__ StencilMmaParams P, const __grid_cons
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) stamp(P, 0);
   constexpr int ndy = NDY, nacc = NACC;      // NDY = 2R + 1; NACC = 2: Sobel's gx and gy
-  // TS: the A operand goes through TMEM (columns 256..383 hold 16 K slices), the ring is two chunks
-  constexpr int ring = TS ? 256 : kSmRing / nacc;      // columns per accumulator
+  constexpr int ring = kSmRing / nacc;      // columns per accumulator
   constexpr int ring_chunks = ring / 128;   // 4 or 2
   const int W = P.W3 / P.cs;
 
@@ -316,9 +302,14 @@ stencil_mma_kernel(const __grid_constant__ StencilMmaParams P, const __grid_cons
       if (lane == 0) stamp(P, 2);
       const uint32_t b_lo_base = b_desc_lo(smem_u32(bmat));
       const bool leader = elect_one() && !(P.dbg & 4);
+      uint32_t zmask = 0;        // bit m: row m of the stencil (accumulator-major) has no non-zero weight
+      for (int m = 0; m < nacc * ndy; ++m) {
+        bool any = false;
+        for (int i = 0; i < ndy; ++i) any = any || P.w[m / ndy][m % ndy][i] != 0;
+        if (!any) zmask |= 1u << m;
+      }
       const bool commit_leader = elect_one();
       uint32_t n = 0, C = 0;     // slabs consumed, chunks started
-      uint32_t a_slot = 0;       // TS: K slices copied into TMEM so far
       uint32_t acquired = 0;     // chunk positions whose previous contents the epilogue has released
       int g = g_lo;
       Run r;
@@ -356,31 +347,20 @@ stencil_mma_kernel(const __grid_constant__ StencilMmaParams P, const __grid_cons
           {
             const uint32_t a_lo_slab = a_desc_lo(smem_u32(slab));
             // 2R+1 (x2 for Sobel) MMAs of one K-step: result columns [rc, rc + n) of the ring, rc + n <= ring
-            auto mma1 = [&](uint32_t d, uint32_t a_lo, uint32_t b_lo, uint32_t id, bool copy) {
-              if constexpr (TS) {
-                const uint32_t ta = tmem + 256 + 8 * (a_slot & 15);
-                if (copy) tmem_cp_128x256b(ta, a_lo, kADescHi);
-                umma_i8_ts(d, ta, b_lo, kBDescHi, id);
-              } else {
-                umma_i8_w(d, a_lo, kADescHi, b_lo, kBDescHi, id);
-              }
-            };
-            // 2R+1 (x2 for Sobel) MMAs of one K-step: result columns [rc, rc + n) of the ring, rc + n <= ring
-            auto issue = [&](uint32_t a_lo, uint32_t b_lo, uint32_t rc, int n, bool copy = true) {
+            // 2R+1 (x2 for Sobel) MMAs of one K-step: result columns [rc, rc + n) of the ring, rc + n <= ring.
+            // Rows of the stencil that are all zero (Sobel's gy has one) are skipped.
+            auto issue = [&](uint32_t a_lo, uint32_t b_lo, uint32_t rc, int n) {
               const uint32_t id = idesc_i8(n);
 #pragma unroll
-              for (int m = 0; m < nacc * ndy; ++m) {
-                if (leader) mma1(tmem + (m / ndy) * ring + rc, a_lo + (m % ndy) * (128 >> 4), b_lo + m * (kSmBBytes >> 4), id, copy);
-                ++a_slot;
-              }
+              for (int m = 0; m < nacc * ndy; ++m)
+                if (leader && !(zmask >> m & 1))
+                  umma_i8_w(tmem + (m / ndy) * ring + rc, a_lo + (m % ndy) * (128 >> 4), kADescHi,
+                            b_lo + m * (kSmBBytes >> 4), kBDescHi, id);
             };
             auto issue_wrap = [&](uint32_t a_lo, uint32_t b_lo, uint32_t rc, int n) {  // split where the ring wraps
               const int n1 = min(n, ring - (int)rc);
               issue(a_lo, b_lo, rc, n1);
-              if (n > n1) {
-                a_slot -= nacc * ndy;   // the second part reads the same K slices
-                issue(a_lo, b_lo + (n1 >> 3) * (256 >> 4), 0, n - n1, false);
-              }
+              if (n > n1) issue(a_lo, b_lo + (n1 >> 3) * (256 >> 4), 0, n - n1);
             };
             auto acquire = [&](uint32_t c_hi) {  // the epilogue has released the ring positions of chunks <= c_hi
               while (acquired <= c_hi) {
@@ -403,12 +383,12 @@ stencil_mma_kernel(const __grid_constant__ StencilMmaParams P, const __grid_cons
                 const uint32_t ra = (rc0 + 32 * ia) & (ring - 1), rb = (rc0 + 32 * ib) & (ring - 1);
 #pragma unroll
                 for (int m = 0; m < nacc * ndy; ++m) {
-                  if (leader) mma1(tmem + (m / ndy) * ring + ra, a_lo_slab + 2 * ia + (m % ndy) * (128 >> 4),
-                                   b_lo_base + m * (kSmBBytes >> 4), id, true);
-                  ++a_slot;
-                  if (leader) mma1(tmem + (m / ndy) * ring + rb, a_lo_slab + 2 * ib + (m % ndy) * (128 >> 4),
-                                   b_lo_base + m * (kSmBBytes >> 4), id, true);
-                  ++a_slot;
+                  if (leader && !(zmask >> m & 1)) {
+                    umma_i8_w(tmem + (m / ndy) * ring + ra, a_lo_slab + 2 * ia + (m % ndy) * (128 >> 4), kADescHi,
+                              b_lo_base + m * (kSmBBytes >> 4), kBDescHi, id);
+                    umma_i8_w(tmem + (m / ndy) * ring + rb, a_lo_slab + 2 * ib + (m % ndy) * (128 >> 4), kADescHi,
+                              b_lo_base + m * (kSmBBytes >> 4), kBDescHi, id);
+                  }
                 }
               };
               if (cpos == 0 || (P.dbg & 32)) {       // window 0 straddles the end of the ring: in two parts
@@ -574,14 +554,13 @@ stencil_mma_kernel(const __grid_constant__ StencilMmaParams P, const __grid_cons
 
 cudaError_t launch_stencil_mma(const StencilMmaParams& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
                                int grid, cudaStream_t stream) {
-  static bool configured[64][5] = {{false}};
+  static bool configured[64][3] = {{false}};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   using Kern = void (*)(StencilMmaParams, CUtensorMap, CUtensorMap);
-  static const Kern table[5] = {stencil_mma_kernel<3, 1, false>, stencil_mma_kernel<5, 1, false>, stencil_mma_kernel<3, 2, false>,
-                                stencil_mma_kernel<3, 1, true>, stencil_mma_kernel<5, 1, true>};
-  const int variant = P.mode == SM_SOBEL ? 2 : (P.R == 2 ? 1 : 0) + ((P.dbg & 64) ? 3 : 0);
+  static const Kern table[3] = {stencil_mma_kernel<3, 1>, stencil_mma_kernel<5, 1>, stencil_mma_kernel<3, 2>};
+  const int variant = P.mode == SM_SOBEL ? 2 : P.R == 2 ? 1 : 0;
   if (P.mode == SM_SOBEL && P.R != 1) return cudaErrorInvalidValue;
   const Kern kern = table[variant];
   const int smem = kSmStages * kSmSlabBytes + kSmVariants * 2 * 3 * kSmBBytes + 2 * kSmOutBytes + 1024;

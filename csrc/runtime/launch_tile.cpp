@@ -109,10 +109,17 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
     const int need_a = std::max(0, y0 - seg.halo), need_b = std::min(L.H, y1 + seg.halo);
     B2I_CHECK_ARG(src.y_begin <= need_a && src.y_end >= need_b && dst.y_begin <= y0 && dst.y_end >= y1,
                   "views do not cover the band [%d,%d) and its halo", y0, y1);
+    // Measured on 8K RGB (scripts/kbench.py): gauss5 54.7 us on the separable sweep, 55.1 on the
+    // tensor-core kernel; gauss3 44.1 vs 47.6; Sobel 55.1 vs 75. So 3-channel Gaussians and Sobel go
+    // to the sweeps, and the tensor-core kernel takes what they cannot: one-channel planes, widths
+    // that are not multiples of 8 pixels, and every stencil that is not separable (the tile kernel
+    // needs 130 us and more for those). B200IMG_PREFER_MMA=1 turns the order around.
+    static const int prefer_mma = env_int("B200IMG_PREFER_MMA", 0);
     int sw = try_sweep(plan, seg, L, y0, y1, src, dst, sms, last);
-    if (sw == 0) sw = try_stencil_mma(plan, seg, L, y0, y1, src, dst, sms, first, last);
+    if (sw == 0 && prefer_mma) sw = try_stencil_mma(plan, seg, L, y0, y1, src, dst, sms, first, last);
     if (sw == 0) sw = try_sweep5(plan, seg, L, y0, y1, src, dst, sms, first, last);
     if (sw == 0) sw = try_sweep_sobel(plan, seg, L, y0, y1, src, dst, sms, first, last);
+    if (sw == 0) sw = try_stencil_mma(plan, seg, L, y0, y1, src, dst, sms, first, last);
     if (sw < 0) return B2I_ERR_CUDA;
     if (sw > 0) return B2I_OK;
   }

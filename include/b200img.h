@@ -234,8 +234,10 @@ int b2i_cuda_run_image(b2i_plan_t* plan, uint64_t src, int64_t src_pitch, uint64
  *    rejected with B2I_ERR_UNSUPPORTED and a message naming the limit. The array is
  *    B2I_NOALLOC_SCRATCH_BYTES (about 12 MiB) and every GPU that loads the library holds it
  *    until the process exits.
- *  - The first call on each device looks up the array's device address (and performs the
- *    kernels' one-time attribute set-up); make that first call before any stream capture.
+ *  - The first call on each device loads the module that holds the array (and performs the
+ *    kernels' one-time attribute set-up); make that first call before any stream capture. The
+ *    array's device address is looked up on every call (no allocation), so a cudaDeviceReset
+ *    between calls is harmless.
  *  - All calls on a device share the one array. A call never depends on what an earlier call
  *    left in it (the part that must start clean is cleared on the stream, the rest is written
  *    before it is read), but two calls that overlap on the GPU - different streams, or

@@ -81,8 +81,11 @@ class Plan:
         if out is None:
             shape = (H, W) if (self.cout == 1 and src.ndim == 2) else (H, W, self.cout)
             out = torch.empty(shape, dtype=torch.uint8, device=src.device)
-        elif not out.is_contiguous() or out.numel() != H * W * self.cout:
-            raise ValueError("out must be a contiguous tensor of H*W*cout bytes")
+        elif out.numel() != H * W * self.cout or out.dtype != torch.uint8:
+            raise ValueError("out must be a uint8 tensor of H*W*cout bytes")
+        elif not out.is_contiguous() and not (out.ndim == 3 and out.stride(2) == 1 and out.stride(1) == self.cout):
+            raise ValueError("out must be contiguous, or rows of packed pixels at a row pitch (see pitched_empty)")
+        dst_pitch = W * self.cout if out.is_contiguous() else out.stride(0)
         flags = (_lib.LAUNCH_NAIVE if naive else 0) | (_lib.LAUNCH_NO_TMA if no_tma else 0)
         need_tmp = naive or self.n_segments > 1 or (self.halo > 0 and (W <= 16 or H <= 16))
         t0 = t1 = ls = None
@@ -92,7 +95,7 @@ class Plan:
             L = Launch()
             L.W, L.H, L.y0, L.y1 = W, H, 0, H
             L.src = View(src.data_ptr(), src_pitch, 0, H)
-            L.dst = View(out.data_ptr(), W * self.cout, 0, H)
+            L.dst = View(out.data_ptr(), dst_pitch, 0, H)
             if need_tmp:
                 L.tmp[0] = View(t0.data_ptr(), W * 3, 0, H)
                 L.tmp[1] = View(t1.data_ptr(), W * 3, 0, H)
@@ -102,6 +105,18 @@ class Plan:
             L.flags = flags
             check(lib.b2i_cuda_run(self._p, C.byref(L)))
         return out
+
+
+def pitched_empty(H: int, W: int, Cn: int = 3, device="cuda", align: int = 128) -> torch.Tensor:
+    """An HxWxC uint8 image whose rows start `align` bytes apart-aligned: ``t.stride(0)`` is the pitch.
+
+    TMA (and with it every fast kernel here) needs a 16-byte-aligned row pitch; a tightly packed
+    image has one only when ``W * C`` is a multiple of 16. The reference takes any width
+    (``kernel.cu:116``); images of odd widths should live in buffers like this one, the way
+    ``cudaMallocPitch`` lays them out."""
+    pitch = (W * Cn + align - 1) // align * align
+    buf = torch.empty(H * pitch, dtype=torch.uint8, device=device)
+    return buf.as_strided((H, W, Cn), (pitch, Cn, 1))
 
 
 _PLAN_CACHE = {}

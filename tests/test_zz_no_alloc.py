@@ -22,8 +22,8 @@ from mpi_cuda_imagemanipulation_b200 import _lib
 torch = pytest.importorskip("torch")
 pytestmark = pytest.mark.gpu
 
-# five 5x5 blurs need 10 halo rows: more than one launch can absorb, so the plan has two
-# segments and the intermediate image goes through scratch memory
+# five 5x5 blurs run as several launches (one per blur on the tensor-core kernel, or two fused
+# segments on the tile kernel): the intermediate images go through scratch memory
 MULTI_SEGMENT = "gauss5,gauss5,gauss5,gauss5,gauss5"
 
 
