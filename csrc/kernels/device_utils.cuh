@@ -131,6 +131,28 @@ __device__ __forceinline__ bool wait_flag_ge(const uint32_t* p, uint32_t want,
   }
 }
 
+// The same at GPU scope, for flags written by other SMs of this GPU (task-to-task ordering inside
+// a resident multi-pass kernel).
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ bool wait_flag_ge_gpu(const uint32_t* p, uint32_t want, unsigned long long timeout_ns) {
+  if ((int32_t)(ld_acquire_gpu(p) - want) >= 0) return true;
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  for (;;) {
+    if ((int32_t)(ld_acquire_gpu(p) - want) >= 0) return true;
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    if (t - t0 > timeout_ns) return false;
+  }
+}
+
 // End of a sweep kernel (lane 0 of every warp that had work, after its stores have completed): the
 // last warp to arrive waits for the other GPUs' done flags (the root's side) and / or publishes this
 // GPU's done flag (everyone else's side) -- MPI_Gather's completion (kernel.cu:223) without a

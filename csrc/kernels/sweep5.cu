@@ -93,7 +93,8 @@ __device__ __forceinline__ void vacc(uint32_t (&acc)[12], const uint32_t (&h)[12
 template <bool MG, bool FIVE, bool BINOM>
 __global__ void __launch_bounds__(kS5Warps * 32, kS5CtasPerSm)
 sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CUtensorMap src_map,
-              const __grid_constant__ CUtensorMap dst_map) {
+              const __grid_constant__ CUtensorMap dst_map, const __grid_constant__ CUtensorMap src_map1,
+              const __grid_constant__ CUtensorMap dst_map1) {
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ __align__(256) uint8_t lut1[256];
   __shared__ __align__(8) uint64_t bars[kS5Warps * NST];
@@ -124,6 +125,15 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
 
   uint32_t n_in = 0, n_out = 0;  // boxes consumed / stored by this warp so far
   const int total_warps = gridDim.x * kS5Warps;
+  // Resident multi-pass launches walk the passes here; every other launch is one pass.
+  const int n_passes = MG ? max(1, P.n_passes) : 1;
+  for (int pass = 0; pass < n_passes; ++pass) {
+  const bool odd = MG && (pass & 1);
+  const CUtensorMap* const smap = odd ? &src_map1 : &src_map;
+  const CUtensorMap* const dmap = odd ? &dst_map1 : &dst_map;
+  const bool multi = MG && n_passes > 1;
+  const bool wait_nb = MG && (!multi || pass > 0);             // ghost rows of pass 0 come from the scatter
+  const bool push_nb = MG && (!multi || pass + 1 < n_passes);  // nobody reads the last pass's halo
   for (int task = blockIdx.x * kS5Warps + warp; task < P.n_tasks; task += total_warps) {
     // boundary segments first: their rows feed the neighbours' next pass
     const int so = task / P.n_strips, strip = task - so * P.n_strips;
@@ -136,14 +146,30 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
     const int xw_in = (xs * 3 - 32) >> 2, xw_out = (xs * 3) >> 2;
     // A task that reads ghost rows, or writes the neighbour's, first sees the neighbour's flag of
     // the previous pass: its rows have landed here and it has finished reading what we overwrite.
-    const bool sig_up = MG && P.signal_up_flag && ya < P.y0 + P.push_rows;
-    const bool sig_dn = MG && P.signal_dn_flag && yb > P.y1 - P.push_rows;
+    const bool sig_up = push_nb && P.signal_up_flag && ya < P.y0 + P.push_rows;
+    const bool sig_dn = push_nb && P.signal_dn_flag && yb > P.y1 - P.push_rows;
+    if (multi && pass > 0) {
+      // the tasks around this one (strips s-1..s+1 x segments seg-1..seg+1) have finished the pass
+      // before: their rows are what this task reads, and they have read what it overwrites
+      if (lane < 9) {
+        const int ds = lane % 3 - 1, dg = lane / 3 - 1;
+        const int s2 = strip + ds, g2 = seg + dg;
+        if (s2 >= 0 && s2 < P.n_strips && g2 >= 0 && g2 < P.n_segs) {
+          const int so2 = g2 == 0 ? 0 : g2 == P.n_segs - 1 ? 1 : g2 + 1;
+          if (!wait_flag_ge_gpu(reinterpret_cast<const uint32_t*>(P.task_done) + so2 * P.n_strips + s2,
+                                P.wait_epoch + (uint32_t)pass, P.timeout_ns))
+            atomicExch(reinterpret_cast<uint32_t*>(P.status), 4u);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) asm volatile("fence.proxy.async;" ::: "memory");  // the flags (generic proxy) before the TMA loads
+    }
     if (lane == 0) {
-      if (MG) sweep_wait_neighbours(P, ya, yb, 2, sig_up, sig_dn);
+      if (wait_nb) sweep_wait_neighbours(P, ya, yb, 2, sig_up, sig_dn, (uint32_t)pass);
       for (int c = 0; c < min(NST, n_chunks); ++c) {
         const uint32_t st = (n_in + c) % NST;
         mbar_arrive_expect_tx(&bar[st], CH * kS5InBytes);
-        tma_load_2d(in_ring + st * P.in_stage_bytes, &src_map, xw_in, ya - 2 + c * CH - P.src_y_begin, &bar[st]);
+        tma_load_2d(in_ring + st * P.in_stage_bytes, smap, xw_in, ya - 2 + c * CH - P.src_y_begin, &bar[st]);
       }
     }
     const bool left_edge = x0 == 0, right_edge = x0 + 8 == P.W, beyond = x0 < 0 || x0 >= P.W;
@@ -253,8 +279,8 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
           d[1] = make_uint2(r[2], r[3]);
           d[2] = make_uint2(r[4], r[5]);
         }
-        if (MG && P.push_rows && !halo_lane && !beyond)  // halo rows also go into the neighbours' ghost rows
-          sweep_push_row(P, y - 2, (int64_t)xs * 3 + (lane - 1) * 24, r);
+        if (push_nb && P.push_rows && !halo_lane && !beyond)  // halo rows also go into the neighbours' ghost rows
+          sweep_push_row(P, y - 2, (int64_t)xs * 3 + (lane - 1) * 24, r, odd);
         if (MG && P.plain_dst_ptr && (er == 4 || u == steps - 1)) {
           // NVLS: the box leaves in coalesced 16-byte stores to the multicast image, one store per
           // byte, and the switch writes every GPU's copy
@@ -268,7 +294,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            tma_store_2d(&dst_map, xw_out, ya + ec * CH - P.y0, out_ring + ob * P.out_buf_bytes);
+            tma_store_2d(dmap, xw_out, ya + ec * CH - P.y0, out_ring + ob * P.out_buf_bytes);
             tma_store_commit();
           }
         }
@@ -290,30 +316,42 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
       __syncwarp();  // every lane has read the box: the stage can take box c + NST
       if (lane == 0 && c + NST < n_chunks) {
         mbar_arrive_expect_tx(&bar[st], CH * kS5InBytes);
-        tma_load_2d(in_ring + st * P.in_stage_bytes, &src_map, xw_in, ya - 2 + (c + NST) * CH - P.src_y_begin,
+        tma_load_2d(in_ring + st * P.in_stage_bytes, smap, xw_in, ya - 2 + (c + NST) * CH - P.src_y_begin,
                     &bar[st]);
       }
     }
     n_in += n_chunks;
     n_out += (yb - ya + CH - 1) / CH;
-    if (sig_up || sig_dn) sweep_signal_neighbours(P, sig_up, sig_dn, lane);
+    if (sig_up || sig_dn) sweep_signal_neighbours(P, sig_up, sig_dn, lane, (uint32_t)pass);
+    if (multi && pass + 1 < n_passes) {
+      // this task's rows of the pass are in memory: publish it to the tasks around it
+      __syncwarp();
+      if (lane == 0) {
+        tma_store_wait_all();
+        asm volatile("fence.proxy.async;" ::: "memory");
+        st_release_gpu(reinterpret_cast<uint32_t*>(P.task_done) + task, P.wait_epoch + (uint32_t)pass + 1);
+      }
+    }
+  }
   }
   sweep_kernel_end(P, blockIdx.x * kS5Warps + warp, total_warps, lane);
 }
 
 }  // namespace
 
+// src_map1 / dst_map1: the other direction of a resident multi-pass launch (P.n_passes > 1), which
+// is launched cooperatively: its tasks wait for one another, so every CTA has to be resident.
 cudaError_t launch_sweep5(const Sweep5Params& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
-                          int grid, cudaStream_t stream) {
+                          int grid, cudaStream_t stream, const CUtensorMap* src_map1, const CUtensorMap* dst_map1) {
   static bool configured[64][8] = {{false}};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   const bool mg = P.push_rows || P.wait_up_flag || P.wait_dn_flag || P.signal_up_flag || P.signal_dn_flag ||
-                  P.plain_dst_ptr;
+                  P.plain_dst_ptr || P.n_passes > 1;
   const bool five = (P.wh[0] | P.wh[4]) != 0;
   const int variant = (mg ? 4 : 0) + (five ? 2 : 0) + (P.binom ? 1 : 0);
-  using Kern = void (*)(Sweep5Params, CUtensorMap, CUtensorMap);
+  using Kern = void (*)(Sweep5Params, CUtensorMap, CUtensorMap, CUtensorMap, CUtensorMap);
   static const Kern table[8] = {
       sweep5_kernel<false, false, false>, sweep5_kernel<false, false, true>, sweep5_kernel<false, true, false>,
       sweep5_kernel<false, true, true>,   sweep5_kernel<true, false, false>, sweep5_kernel<true, false, true>,
@@ -324,7 +362,13 @@ cudaError_t launch_sweep5(const Sweep5Params& P, const CUtensorMap& src_map, con
     if (e != cudaSuccess) return e;
     configured[dev][variant] = true;
   }
-  kern<<<grid, kS5Warps * 32, P.warp_smem * kS5Warps, stream>>>(P, src_map, dst_map);
+  if (P.n_passes > 1) {
+    if (!src_map1 || !dst_map1) return cudaErrorInvalidValue;
+    void* args[5] = {(void*)&P, (void*)&src_map, (void*)&dst_map, (void*)src_map1, (void*)dst_map1};
+    return cudaLaunchCooperativeKernel((const void*)kern, dim3(grid), dim3(kS5Warps * 32), args,
+                                       (size_t)P.warp_smem * kS5Warps, stream);
+  }
+  kern<<<grid, kS5Warps * 32, P.warp_smem * kS5Warps, stream>>>(P, src_map, dst_map, src_map, dst_map);
   return cudaGetLastError();
 }
 }  // namespace b2i

@@ -38,6 +38,14 @@ struct Sweep5Params {
   // of an NVLS multicast image) instead of the staging buffer + TMA store; 0 = off
   uint64_t plain_dst_ptr;
   int64_t plain_dst_pitch;
+  // resident multi-pass launch (n_passes > 1): the kernel itself walks the passes, ping-ponging
+  // between two band buffers (tensor maps src_map/dst_map on even passes, src_map1/dst_map1 on odd
+  // ones). A task of pass p starts once the (up to nine) tasks around it have finished pass p-1:
+  // task_done[t] holds epoch_base + passes finished. Neighbour GPUs are waited for from pass 1 on
+  // (wait_epoch + p) and signalled after every pass but the last (signal_epoch + p).
+  int32_t n_passes, reserved1;
+  uint64_t task_done;                      // u32 per task in local memory, only ever growing
+  uint64_t push_up_ptr_odd, push_dn_ptr_odd;  // the push targets of odd passes (the other buffer)
   uint8_t lut1[256];
 };
 

@@ -3,6 +3,7 @@
 // neighbour flags and epochs, push pointers, counters, the status word and the timeout.
 #pragma once
 #include "device_utils.cuh"
+#include "sweep5.hpp"
 
 namespace b2i {
 namespace dev {
@@ -13,14 +14,14 @@ namespace dev {
 // task's own rows.
 template <class Params>
 __device__ __forceinline__ void sweep_wait_neighbours(const Params& P, int ya, int yb, int reach, bool sig_up,
-                                                      bool sig_dn) {
+                                                      bool sig_dn, uint32_t pass = 0) {
   if (P.wait_up_flag && (ya - reach < P.y0 || sig_up)) {
-    if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_up_flag), P.wait_epoch, P.timeout_ns))
+    if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_up_flag), P.wait_epoch + pass, P.timeout_ns))
       atomicExch(reinterpret_cast<uint32_t*>(P.status), 1u);
     asm volatile("fence.proxy.async;" ::: "memory");  // the flag (generic proxy) before TMA loads of the ghost rows
   }
   if (P.wait_dn_flag && (yb + reach > P.y1 || sig_dn)) {
-    if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_dn_flag), P.wait_epoch, P.timeout_ns))
+    if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_dn_flag), P.wait_epoch + pass, P.timeout_ns))
       atomicExch(reinterpret_cast<uint32_t*>(P.status), 2u);
     asm volatile("fence.proxy.async;" ::: "memory");
   }
@@ -30,15 +31,24 @@ __device__ __forceinline__ void sweep_wait_neighbours(const Params& P, int ya, i
 // of the band also go straight from registers into the neighbours' ghost rows (peer or IPC memory).
 // `col` = byte offset of the lane's pixels in the row.
 template <class Params>
-__device__ __forceinline__ void sweep_push_row(const Params& P, int oy, int64_t col, const uint32_t (&r)[6]) {
-  if (P.push_up_ptr && oy < P.y0 + P.push_rows) {
-    uint2* g = reinterpret_cast<uint2*>(P.push_up_ptr + (int64_t)(oy - P.y0) * P.push_pitch + col);
+__device__ __forceinline__ void sweep_push_row(const Params& P, int oy, int64_t col, const uint32_t (&r)[6],
+                                               bool odd = false) {
+  // (resident multi-pass launches push into the other band buffer on odd passes: sweep5.hpp)
+  uint64_t up = P.push_up_ptr, dn = P.push_dn_ptr;
+  if constexpr (sizeof(Params) == sizeof(Sweep5Params)) {
+    if (odd) {
+      up = reinterpret_cast<const Sweep5Params&>(P).push_up_ptr_odd;
+      dn = reinterpret_cast<const Sweep5Params&>(P).push_dn_ptr_odd;
+    }
+  }
+  if (up && oy < P.y0 + P.push_rows) {
+    uint2* g = reinterpret_cast<uint2*>(up + (int64_t)(oy - P.y0) * P.push_pitch + col);
     g[0] = make_uint2(r[0], r[1]);
     g[1] = make_uint2(r[2], r[3]);
     g[2] = make_uint2(r[4], r[5]);
   }
-  if (P.push_dn_ptr && oy >= P.y1 - P.push_rows) {
-    uint2* g = reinterpret_cast<uint2*>(P.push_dn_ptr + (int64_t)(oy - (P.y1 - P.push_rows)) * P.push_pitch + col);
+  if (dn && oy >= P.y1 - P.push_rows) {
+    uint2* g = reinterpret_cast<uint2*>(dn + (int64_t)(oy - (P.y1 - P.push_rows)) * P.push_pitch + col);
     g[0] = make_uint2(r[0], r[1]);
     g[1] = make_uint2(r[2], r[3]);
     g[2] = make_uint2(r[4], r[5]);
@@ -47,19 +57,23 @@ __device__ __forceinline__ void sweep_push_row(const Params& P, int oy, int64_t 
 
 // Whole warp, after a task that pushed rows: count the task in; the last task of each side releases
 // the neighbour's flag (the counters are left zeroed for the next pass).
+// `pass`: resident multi-pass launches count even and odd passes apart (boundary tasks of one side
+// are never more than one pass apart: each waits for the neighbour, which waits for all of them),
+// and the epoch they publish grows with the pass.
 template <class Params>
-__device__ __forceinline__ void sweep_signal_neighbours(const Params& P, bool sig_up, bool sig_dn, int lane) {
+__device__ __forceinline__ void sweep_signal_neighbours(const Params& P, bool sig_up, bool sig_dn, int lane,
+                                                        uint32_t pass = 0) {
   __threadfence_system();  // every lane's pushes
   __syncwarp();
   if (lane != 0) return;
-  uint32_t* counters = reinterpret_cast<uint32_t*>(P.counters);
+  uint32_t* counters = reinterpret_cast<uint32_t*>(P.counters) + (pass & 1) * 4;
   if (sig_up && atomicAdd(&counters[0], 1u) + 1 == (uint32_t)P.n_up_tasks) {
     atomicExch(&counters[0], 0u);
-    st_release_sys(reinterpret_cast<uint32_t*>(P.signal_up_flag), P.signal_epoch);
+    st_release_sys(reinterpret_cast<uint32_t*>(P.signal_up_flag), P.signal_epoch + pass);
   }
   if (sig_dn && atomicAdd(&counters[1], 1u) + 1 == (uint32_t)P.n_dn_tasks) {
     atomicExch(&counters[1], 0u);
-    st_release_sys(reinterpret_cast<uint32_t*>(P.signal_dn_flag), P.signal_epoch);
+    st_release_sys(reinterpret_cast<uint32_t*>(P.signal_dn_flag), P.signal_epoch + pass);
   }
 }
 

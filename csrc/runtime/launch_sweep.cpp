@@ -310,3 +310,104 @@ int try_sweep_sobel(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, i
 }
 
 }  // namespace b2i
+
+// ---- resident multi-pass launch -------------------------------------------------------------------
+// `passes` passes of a one-segment separable stencil (the Gaussians) over a resident band in ONE
+// cooperative launch of sweep5_kernel<MG>: the kernel ping-pongs between the two band buffers that
+// `even` (buffer 0 -> 1) and `odd` (1 -> 0) describe, orders its own tasks with one flag per task
+// and its neighbours with the epoch flags (kernels/sweep5.hpp). What stood here before was one
+// launch per pass: at 8 GPUs an 8K band is 540 rows, and launch, pipeline fill and drain cost more
+// than the rows. The reference has neither passes nor halos (kernel.cu:195 embosses bands in
+// isolation between two MPI_Barriers, kernel.cu:127,133).
+extern "C" int b2i_cuda_run_resident_fused(b2i_plan_t* plan, const b2i_launch_t* even, const b2i_launch_t* odd,
+                                           int passes, uint32_t epoch_base, uint64_t task_flags,
+                                           int n_task_flags) {
+  using namespace b2i;
+  B2I_CHECK_ARG(plan && even && odd && passes >= 1 && task_flags, "bad arguments");
+  const b2i_launch_t& L = *even;
+  const std::vector<Segment>& segs = plan->segs_split.empty() ? plan->segs : plan->segs_split;
+  if (segs.size() != 1 || segs[0].phases.size() != 2 || segs[0].phases[0].type != PH_SEPH ||
+      segs[0].phases[1].type != PH_SEPV || segs[0].cin != 3 || segs[0].cout != 3 || segs[0].phases[1].expand ||
+      segs[0].phases[1].lut >= 0)
+    B2I_FAIL(B2I_ERR_UNSUPPORTED, "the fused resident launch takes one separable 3-channel stencil");
+  const Segment& seg = segs[0];
+  const PhaseDesc& ph = seg.phases[0];
+  const PhaseDesc& pv = seg.phases[1];
+  const int y0 = L.y0, y1 = L.y1;
+  if ((L.W & 7) || L.W < 16 || L.H < 8 || y1 - y0 < 1 || odd->y0 != y0 || odd->y1 != y1 ||
+      !tensor_map_encoder())
+    B2I_FAIL(B2I_ERR_UNSUPPORTED, "geometry the sweep kernel does not take");
+  bool pushes = false, flags = false;
+  if (!sweep_hooks_ok(L, y0, y1, true, true, &pushes, &flags) || !(L.counters && L.status))
+    B2I_FAIL(B2I_ERR_UNSUPPORTED, "multi-GPU hooks the sweep kernel does not take");
+  int dev = 0, sms = 0;
+  B2I_CUDA(cudaGetDevice(&dev));
+  B2I_TRY(device_sms(dev, &sms));
+  Sweep5Params P;
+  memset(&P, 0, sizeof P);
+  P.W = L.W;
+  P.H = L.H;
+  P.y0 = y0;
+  P.y1 = y1;
+  P.src_y_begin = L.src.y_begin;
+  P.border = ph.border;
+  const int up = 8 - pv.shift;
+  if (up < 0) B2I_FAIL(B2I_ERR_UNSUPPORTED, "shift beyond 8");
+  P.bias = pv.bias << up;
+  const int off = ph.ksize == 5 ? 0 : 1;
+  for (int i = 0; i < ph.ksize; ++i) {
+    P.wh[i + off] = ph.sep[i];
+    P.wv[i + off] = pv.sep[i] << up;
+  }
+  static const int b5[5] = {1, 4, 6, 4, 1}, b3[5] = {0, 1, 2, 1, 0};
+  P.binom = !memcmp(P.wh, b5, sizeof b5) || !memcmp(P.wh, b3, sizeof b3);
+  P.in_stage_bytes = align_up(kS5Chunk * kS5InBytes, 128);
+  P.out_buf_bytes = align_up(kS5Chunk * kS5OutBytes, 128);
+  P.warp_smem = kS5Stages * P.in_stage_bytes + 2 * P.out_buf_bytes + 128;
+  CUtensorMap sm0, dm0, sm1, dm1;
+  auto maps = [&](const b2i_launch_t& X, CUtensorMap* sm, CUtensorMap* dm) {
+    if (X.src.y_begin != L.src.y_begin || X.src.y_end != L.src.y_end) return false;
+    const int src_rows = std::min(X.src.y_end, L.H) - X.src.y_begin;
+    if (!encode_map(sm, X.src.ptr, X.src.pitch, (int64_t)L.W * 3, src_rows, kS5InBytes, kS5Chunk)) return false;
+    const uint64_t dptr = X.dst.ptr + (uint64_t)((int64_t)(y0 - X.dst.y_begin) * X.dst.pitch);
+    return encode_map(dm, dptr, X.dst.pitch, (int64_t)L.W * 3, y1 - y0, kS5OutBytes, kS5Chunk);
+  };
+  if (!maps(*even, &sm0, &dm0) || !maps(*odd, &sm1, &dm1))
+    B2I_FAIL(B2I_ERR_UNSUPPORTED, "band buffers the tensor maps do not take");
+  P.n_strips = (L.W + kS5Strip - 1) / kS5Strip;
+  const int resident = sms * kS5CtasPerSm * kS5Warps;
+  P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kS5Chunk, 5, 120, 4);
+  P.n_segs = (y1 - y0 + P.seg_rows - 1) / P.seg_rows;
+  P.n_tasks = P.n_strips * P.n_segs;
+  if (P.n_tasks + 8 > n_task_flags)
+    B2I_FAIL(B2I_ERR_ARG, "%d task flags given, %d needed", n_task_flags, P.n_tasks + 8);
+  sweep_hooks_fill(P, L, y0, y1, true, true, pushes);
+  if (pushes) {   // odd passes push into the other buffer of the neighbours
+    if (odd->push_up.ptr)
+      P.push_up_ptr_odd = odd->push_up.ptr + (uint64_t)((int64_t)(y0 - odd->push_up.y_begin) * odd->push_up.pitch);
+    if (odd->push_dn.ptr)
+      P.push_dn_ptr_odd =
+          odd->push_dn.ptr + (uint64_t)((int64_t)(y1 - L.push_rows - odd->push_dn.y_begin) * odd->push_dn.pitch);
+  }
+  if (passes == 1) {   // a single pass reads what the scatter left and nobody reads its halo
+    P.wait_up_flag = P.wait_dn_flag = P.signal_up_flag = P.signal_dn_flag = 0;
+    P.push_up_ptr = P.push_dn_ptr = 0;
+    P.push_rows = 0;
+  }
+  P.n_passes = passes;
+  P.wait_epoch = epoch_base;
+  P.signal_epoch = epoch_base + 1;
+  P.task_done = task_flags;
+  P.counters = task_flags + 4ull * (uint64_t)P.n_tasks;   // eight zeroed words behind the task flags
+  const int grid = std::max(1, std::min((P.n_tasks + kS5Warps - 1) / kS5Warps, sms * kS5CtasPerSm));
+  plan->info.last_tile_h = -P.seg_rows;
+  plan->info.last_smem_bytes = P.warp_smem * kS5Warps;
+  plan->info.last_grid = grid;
+  plan->info.last_blocks_per_sm = kS5CtasPerSm;
+  plan->info.last_tma_load = plan->info.last_tma_store = 1;
+  plan->info.last_launches = 1;
+  cudaError_t e = passes > 1 ? launch_sweep5(P, sm0, dm0, grid, (cudaStream_t)L.stream, &sm1, &dm1)
+                             : launch_sweep5(P, sm0, dm0, grid, (cudaStream_t)L.stream);
+  if (e != cudaSuccess) B2I_FAIL(B2I_ERR_CUDA, "fused resident launch: %s", cudaGetErrorString(e));
+  return B2I_OK;
+}

@@ -22,7 +22,8 @@ cudaError_t launch_tile_chain(const TileParams& P, const CUtensorMap& src_map,
 cudaError_t tile_chain_occupancy(int smem_bytes, int* blocks_per_sm);
 cudaError_t launch_pointwise(const PointwiseParams& P, int grid, cudaStream_t stream);
 cudaError_t launch_sweep5(const Sweep5Params& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
-                          int grid, cudaStream_t stream);
+                          int grid, cudaStream_t stream, const CUtensorMap* src_map1 = nullptr,
+                          const CUtensorMap* dst_map1 = nullptr);
 cudaError_t launch_sweep_sobel(const SweepSobelParams& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,
                                int grid, cudaStream_t stream);
 cudaError_t launch_sweep3(const SweepParams& P, const CUtensorMap& src_map, const CUtensorMap& dst_map,

@@ -342,6 +342,14 @@ int b2i_cuda_run_steps(b2i_plan_t* plan, const b2i_launch_t* launch, int steps, 
  * descriptions, halo flags waited/signalled with epochs epoch_base+p / epoch_base+p+1. */
 int b2i_cuda_run_resident_steps(b2i_plan_t* plan, const b2i_launch_t* even, const b2i_launch_t* odd,
                                 int passes, uint32_t epoch_base);
+/* The same passes in ONE cooperative kernel launch (one separable 3-channel stencil, e.g. gauss5):
+ * the kernel walks the passes itself, tasks wait for the tasks around them through `task_flags`
+ * (n_task_flags u32 of local device memory, zeroed once when allocated and only ever growing:
+ * at least tasks + 8, 16384 is plenty) and for the neighbour GPUs through the epoch flags.
+ * B2I_ERR_UNSUPPORTED if the plan or the buffers do not fit (use b2i_cuda_run_resident_steps).
+ * The halo exchange the reference never had (kernel.cu:195) without its MPI_Barriers (kernel.cu:127,133). */
+int b2i_cuda_run_resident_fused(b2i_plan_t* plan, const b2i_launch_t* even, const b2i_launch_t* odd, int passes,
+                                uint32_t epoch_base, uint64_t task_flags, int n_task_flags);
 int b2i_cuda_memcpy2d(uint64_t dst, size_t dpitch, uint64_t src, size_t spitch, size_t width,
                       size_t height, int kind /*0 H2D, 1 D2H, 2 D2D*/, void* stream);
 

@@ -18,6 +18,7 @@ LIB_PATH = os.environ.get("B200IMG_LIB") or os.path.join(_HERE, "lib", "libb200i
 
 B2I_MAX_OPS = 16
 B2I_MAX_GPUS = 16
+B2I_ERR_UNSUPPORTED = -4
 
 # b2i_status
 OK, ERR_ARG, ERR_IO, ERR_CUDA, ERR_UNSUPPORTED, ERR_NO_DEVICE, ERR_TIMEOUT, ERR_NOMEM = (
@@ -201,5 +202,7 @@ _sig("b2i_cuda_set_flags", C.c_int, _P(C.c_uint64), C.c_int, C.c_uint32, C.c_voi
 _sig("b2i_cuda_run_steps", C.c_int, C.c_void_p, _P(Launch), C.c_int, C.c_uint32, _P(C.c_uint64), C.c_int,
      C.c_uint64)
 _sig("b2i_cuda_run_resident_steps", C.c_int, C.c_void_p, _P(Launch), _P(Launch), C.c_int, C.c_uint32)
+_sig("b2i_cuda_run_resident_fused", C.c_int, C.c_void_p, _P(Launch), _P(Launch), C.c_int, C.c_uint32, C.c_uint64,
+     C.c_int)
 _sig("b2i_cuda_memcpy2d", C.c_int, C.c_uint64, C.c_size_t, C.c_uint64, C.c_size_t, C.c_size_t, C.c_size_t,
      C.c_int, C.c_void_p)

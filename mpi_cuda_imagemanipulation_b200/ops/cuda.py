@@ -107,6 +107,36 @@ class Plan:
         return out
 
 
+def run_passes(plan: "Plan", img: torch.Tensor, passes: int, fused: bool = True) -> torch.Tensor:
+    """`passes` applications of a one-stencil plan to a whole image on one GPU, ping-ponging between
+    two buffers: with fused=True in ONE cooperative launch whose tasks order themselves with
+    per-task flags (the single-GPU form of ``DistRuntime.run_resident``), else one launch per pass."""
+    H, W, Cn = image_geometry(img)
+    bufs = [img.contiguous().clone(), torch.empty_like(img)]
+    words = torch.zeros(64, dtype=torch.int32, device=img.device)
+    flags = torch.zeros(16384, dtype=torch.int32, device=img.device)
+    ls = []
+    with torch.cuda.device(img.device):
+        for k in range(2):
+            L = Launch()
+            L.W, L.H, L.y0, L.y1 = W, H, 0, H
+            L.src = View(bufs[k].data_ptr(), W * Cn, 0, H)
+            L.dst = View(bufs[k ^ 1].data_ptr(), W * Cn, 0, H)
+            L.counters = words.data_ptr()
+            L.status = words.data_ptr() + 16
+            L.stream = torch.cuda.current_stream().cuda_stream
+            ls.append(L)
+        if fused:
+            check(lib.b2i_cuda_run_resident_fused(plan.handle, C.byref(ls[0]), C.byref(ls[1]), passes, 0,
+                                                  flags.data_ptr(), flags.numel()))
+        else:
+            check(lib.b2i_cuda_run_resident_steps(plan.handle, C.byref(ls[0]), C.byref(ls[1]), passes, 0))
+    torch.cuda.synchronize(img.device)
+    if int(words[4].item()) != 0:
+        raise RuntimeError(f"a task wait timed out (status {int(words[4].item())})")
+    return bufs[passes & 1]
+
+
 def pitched_empty(H: int, W: int, Cn: int = 3, device="cuda", align: int = 128) -> torch.Tensor:
     """An HxWxC uint8 image whose rows start `align` bytes apart-aligned: ``t.stride(0)`` is the pitch.
 

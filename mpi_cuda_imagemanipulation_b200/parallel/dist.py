@@ -302,14 +302,31 @@ class DistRuntime:
         L.flags = _lib.LAUNCH_NO_TMA if no_tma else 0
         return L
 
-    def run_resident(self, plan, passes: int, no_tma: bool = False):
+    N_TASK_FLAGS = 16384
+
+    def run_resident(self, plan, passes: int, no_tma: bool = False, fused: bool = True) -> bool:
+        """`passes` applications of the plan's chain to the resident bands, halo rows pushed between
+        the GPUs from inside the kernels. fused=True: ONE cooperative launch that walks the passes
+        itself (``b2i_cuda_run_resident_fused``: one separable 3-channel stencil, e.g. gauss5), else,
+        or when the plan does not fit, one launch per pass. Returns whether the fused launch ran."""
         halo = plan.halo
         if halo > G:
             raise ValueError(f"resident passes support a halo of at most {G} rows per pass")
         even, odd = self._resident_launch(0, halo, no_tma, plan), self._resident_launch(1, halo, no_tma, plan)
+        ran_fused = False
         if self.y1 > self.y0:
-            check(lib.b2i_cuda_run_resident_steps(plan.handle, C.byref(even), C.byref(odd), passes, self.epoch))
+            if fused and not no_tma:
+                if getattr(self, "_task_flags", None) is None:
+                    self._task_flags = torch.zeros(self.N_TASK_FLAGS, dtype=torch.int32, device=self.device)
+                rc = lib.b2i_cuda_run_resident_fused(plan.handle, C.byref(even), C.byref(odd), passes, self.epoch,
+                                                     self._task_flags.data_ptr(), self.N_TASK_FLAGS)
+                if rc != _lib.B2I_ERR_UNSUPPORTED:
+                    check(rc)
+                    ran_fused = True
+            if not ran_fused:
+                check(lib.b2i_cuda_run_resident_steps(plan.handle, C.byref(even), C.byref(odd), passes, self.epoch))
         self.epoch += passes + 1
+        return ran_fused
 
     def gather_resident(self, passes: int, dst_ptr_on_root: int, dst_pitch: int, out_c: int):
         g = self.rgeom

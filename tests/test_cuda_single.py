@@ -174,3 +174,18 @@ def test_pipeline_public_api_on_host_and_device_images():
     assert np.array_equal(pipe(img), want)                                  # numpy in, numpy out
     assert np.array_equal(pipe(torch.from_numpy(img).cuda()).cpu().numpy(), want)   # CUDA tensor, zero-copy
     assert np.array_equal(b2.kern_cpp()(img), b2.host_run("kern_cpp", img))
+
+
+# ---- resident multi-pass launch (one cooperative kernel walks the passes) ------------------------------
+@pytest.mark.parametrize("W,H,passes", [(1920, 1080, 2), (1920, 1080, 5), (7680, 540, 8), (512, 64, 3), (7680, 2160, 4)])
+def test_fused_passes_equal_chained_blurs(W, H, passes):
+    """P passes of gauss5 in one launch (tasks ordered by per-task flags) == gauss5 applied P times."""
+    from mpi_cuda_imagemanipulation_b200.ops.cuda import Plan, run_passes
+    img = b2.synth_image(W, H, 3, seed=9)
+    want = b2.host_run(",".join(["gauss5"] * passes), img)
+    plan = Plan("gauss5", 3)
+    got = run_passes(plan, torch.from_numpy(img).cuda(), passes, fused=True).cpu().numpy()
+    assert plan.info()["launches"] == 1
+    assert np.array_equal(got, want)
+    got2 = run_passes(plan, torch.from_numpy(img).cuda(), passes, fused=False).cpu().numpy()
+    assert np.array_equal(got2, want)
