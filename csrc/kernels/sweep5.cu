@@ -138,7 +138,14 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
     // boundary segments first: their rows feed the neighbours' next pass
     const int so = task / P.n_strips, strip = task - so * P.n_strips;
     const int seg = so == 0 ? 0 : so == 1 ? P.n_segs - 1 : so - 1;
-    const int ya = P.y0 + seg * P.seg_rows, yb = min(P.y1, ya + P.seg_rows);  // output rows [ya, yb)
+    int ya, yb;                                       // output rows [ya, yb)
+    if (MG && P.bseg > 0) {   // short first / last segments: their halo rows are on the way early in the pass
+      ya = seg == 0 ? P.y0 : seg == P.n_segs - 1 ? P.y1 - P.bseg : P.y0 + P.bseg + (seg - 1) * P.seg_rows;
+      yb = seg == 0 ? P.y0 + P.bseg : seg == P.n_segs - 1 ? P.y1 : min(P.y1 - P.bseg, ya + P.seg_rows);
+    } else {
+      ya = P.y0 + seg * P.seg_rows;
+      yb = min(P.y1, ya + P.seg_rows);
+    }
     const int steps = yb - ya + 4;                   // input rows ya-2 .. yb+1
     const int n_chunks = (steps + CH - 1) / CH;
     const int xs = strip * kS5Strip;
@@ -149,10 +156,10 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
     const bool sig_up = push_nb && P.signal_up_flag && ya < P.y0 + P.push_rows;
     const bool sig_dn = push_nb && P.signal_dn_flag && yb > P.y1 - P.push_rows;
     if (multi && pass > 0) {
-      // the tasks around this one (strips s-1..s+1 x segments seg-1..seg+1) have finished the pass
+      // the tasks around this one (strips s-1..s+1 x segments seg-2..seg+2) have finished the pass
       // before: their rows are what this task reads, and they have read what it overwrites
-      if (lane < 9) {
-        const int ds = lane % 3 - 1, dg = lane / 3 - 1;
+      if (lane < 15) {   // two segments up and down: a short remainder segment may lie in between
+        const int ds = lane % 3 - 1, dg = lane / 3 - 2;
         const int s2 = strip + ds, g2 = seg + dg;
         if (s2 >= 0 && s2 < P.n_strips && g2 >= 0 && g2 < P.n_segs) {
           const int so2 = g2 == 0 ? 0 : g2 == P.n_segs - 1 ? 1 : g2 + 1;
@@ -164,8 +171,22 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
       __syncwarp();
       if (lane == 0) asm volatile("fence.proxy.async;" ::: "memory");  // the flags (generic proxy) before the TMA loads
     }
+    if (MG && P.strip_flags && wait_nb) {
+      // per-strip neighbour flags: the three strips above (lanes 0-2) / below (lanes 3-5) this one
+      if (lane < 6) {
+        const bool up = lane < 3;
+        const int s2 = strip + lane % 3 - 1;
+        const uint64_t base = up ? P.wait_up_flag : P.wait_dn_flag;
+        const bool need = up ? (ya - 2 < P.y0 || sig_up) : (yb + 2 > P.y1 || sig_dn);
+        if (base && need && s2 >= 0 && s2 < P.n_strips &&
+            !wait_flag_ge(reinterpret_cast<const uint32_t*>(base) + s2, P.wait_epoch + (uint32_t)pass, P.timeout_ns))
+          atomicExch(reinterpret_cast<uint32_t*>(P.status), up ? 1u : 2u);
+      }
+      __syncwarp();
+      if (lane == 0) asm volatile("fence.proxy.async;" ::: "memory");
+    }
     if (lane == 0) {
-      if (wait_nb) sweep_wait_neighbours(P, ya, yb, 2, sig_up, sig_dn, (uint32_t)pass);
+      if (wait_nb && !(MG && P.strip_flags)) sweep_wait_neighbours(P, ya, yb, 2, sig_up, sig_dn, (uint32_t)pass);
       for (int c = 0; c < min(NST, n_chunks); ++c) {
         const uint32_t st = (n_in + c) % NST;
         mbar_arrive_expect_tx(&bar[st], CH * kS5InBytes);
@@ -181,10 +202,14 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
     for (int i = 0; i < 12; ++i) X0[i] = X1[i] = X2[i] = X3[i] = X4[i] = 0;
 
     // one input row: horizontal pass in registers, then into the five output rows it touches
-    auto step = [&](auto qc, int c, const uint8_t* stage_base, uint32_t ob_prev, uint32_t ob_cur,
+    // SLOW (compile-time): the task also pushes halo rows to a neighbour or stores to a multicast
+    // image. Only the first and last segments of a band do the former, so every other task of a
+    // multi-GPU launch runs the same row loop as the single-GPU kernel.
+    auto step = [&](auto qc, auto slowc, int c, const uint8_t* stage_base, uint32_t ob_prev, uint32_t ob_cur,
                     uint32_t (&K0)[12], uint32_t (&K1)[12], uint32_t (&K2)[12], uint32_t (&K3)[12],
                     uint32_t (&K4)[12]) {
       constexpr int q = decltype(qc)::value;
+      constexpr bool SLOW = MG && decltype(slowc)::value;
       const int u = c * CH + q;
       const int y = ya - 2 + u;
       uint32_t a[10];
@@ -279,9 +304,9 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
           d[1] = make_uint2(r[2], r[3]);
           d[2] = make_uint2(r[4], r[5]);
         }
-        if (push_nb && P.push_rows && !halo_lane && !beyond)  // halo rows also go into the neighbours' ghost rows
+        if (SLOW && push_nb && P.push_rows && !halo_lane && !beyond)  // halo rows also go into the neighbours' ghost rows
           sweep_push_row(P, y - 2, (int64_t)xs * 3 + (lane - 1) * 24, r, odd);
-        if (MG && P.plain_dst_ptr && (er == 4 || u == steps - 1)) {
+        if (SLOW && P.plain_dst_ptr && (er == 4 || u == steps - 1)) {
           // NVLS: the box leaves in coalesced 16-byte stores to the multicast image, one store per
           // byte, and the switch writes every GPU's copy
           const int ec = (u - 4) / CH;
@@ -289,7 +314,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
                        P.plain_dst_ptr + (int64_t)(ya + ec * CH - P.y0) * P.plain_dst_pitch + (int64_t)xs * 3,
                        P.plain_dst_pitch, lane);
         }
-        if (!(MG && P.plain_dst_ptr) && (er == 4 || u == steps - 1)) {  // a box of finished rows leaves by TMA
+        if (!(SLOW && P.plain_dst_ptr) && (er == 4 || u == steps - 1)) {  // a box of finished rows leaves by TMA
           const int ec = (u - 4) / CH;
           fence_proxy_async_smem();
           __syncwarp();
@@ -301,6 +326,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
       }
     };
 
+    auto run_chunks = [&](auto slowc) {
     for (int c = 0; c < n_chunks; ++c) {
       const uint32_t st = (n_in + c) % NST;
       const uint8_t* stage_base = in_ring + st * P.in_stage_bytes;
@@ -308,11 +334,11 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
       const uint32_t ob_prev = (n_out + c + 1) & 1, ob_cur = (n_out + c) & 1;
       const int rows_here = min(CH, steps - c * CH);
       mbar_wait(&bar[st], ((n_in + c) / NST) & 1);
-      step(std::integral_constant<int, 0>{}, c, stage_base, ob_prev, ob_cur, X2, X1, X0, X4, X3);
-      if (rows_here > 1) step(std::integral_constant<int, 1>{}, c, stage_base, ob_prev, ob_cur, X3, X2, X1, X0, X4);
-      if (rows_here > 2) step(std::integral_constant<int, 2>{}, c, stage_base, ob_prev, ob_cur, X4, X3, X2, X1, X0);
-      if (rows_here > 3) step(std::integral_constant<int, 3>{}, c, stage_base, ob_prev, ob_cur, X0, X4, X3, X2, X1);
-      if (rows_here > 4) step(std::integral_constant<int, 4>{}, c, stage_base, ob_prev, ob_cur, X1, X0, X4, X3, X2);
+      step(std::integral_constant<int, 0>{}, slowc, c, stage_base, ob_prev, ob_cur, X2, X1, X0, X4, X3);
+      if (rows_here > 1) step(std::integral_constant<int, 1>{}, slowc, c, stage_base, ob_prev, ob_cur, X3, X2, X1, X0, X4);
+      if (rows_here > 2) step(std::integral_constant<int, 2>{}, slowc, c, stage_base, ob_prev, ob_cur, X4, X3, X2, X1, X0);
+      if (rows_here > 3) step(std::integral_constant<int, 3>{}, slowc, c, stage_base, ob_prev, ob_cur, X0, X4, X3, X2, X1);
+      if (rows_here > 4) step(std::integral_constant<int, 4>{}, slowc, c, stage_base, ob_prev, ob_cur, X1, X0, X4, X3, X2);
       __syncwarp();  // every lane has read the box: the stage can take box c + NST
       if (lane == 0 && c + NST < n_chunks) {
         mbar_arrive_expect_tx(&bar[st], CH * kS5InBytes);
@@ -320,9 +346,25 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
                     &bar[st]);
       }
     }
+    };
+    if (MG && ((push_nb && P.push_rows && (ya < P.y0 + P.push_rows || yb > P.y1 - P.push_rows)) || P.plain_dst_ptr))
+      run_chunks(std::true_type{});
+    else
+      run_chunks(std::false_type{});
     n_in += n_chunks;
     n_out += (yb - ya + CH - 1) / CH;
-    if (sig_up || sig_dn) sweep_signal_neighbours(P, sig_up, sig_dn, lane, (uint32_t)pass);
+    if (MG && P.strip_flags) {
+      if (sig_up || sig_dn) {   // this strip's halo rows are at the neighbour: release its flag for this strip
+        __threadfence_system();
+        __syncwarp();
+        if (lane == 0) {
+          if (sig_up) st_release_sys(reinterpret_cast<uint32_t*>(P.signal_up_flag) + strip, P.signal_epoch + (uint32_t)pass);
+          if (sig_dn) st_release_sys(reinterpret_cast<uint32_t*>(P.signal_dn_flag) + strip, P.signal_epoch + (uint32_t)pass);
+        }
+      }
+    } else if (sig_up || sig_dn) {
+      sweep_signal_neighbours(P, sig_up, sig_dn, lane, (uint32_t)pass);
+    }
     if (multi && pass + 1 < n_passes) {
       // this task's rows of the pass are in memory: publish it to the tasks around it
       __syncwarp();

@@ -43,7 +43,9 @@ struct Sweep5Params {
   // ones). A task of pass p starts once the (up to nine) tasks around it have finished pass p-1:
   // task_done[t] holds epoch_base + passes finished. Neighbour GPUs are waited for from pass 1 on
   // (wait_epoch + p) and signalled after every pass but the last (signal_epoch + p).
-  int32_t n_passes, reserved1;
+  int32_t n_passes;
+  int32_t strip_flags;       // the neighbour flags are per-strip arrays (B2I_LAUNCH_STRIP_FLAGS)
+  int32_t bseg, reserved1;   // > 0: the first and the last segment are bseg rows (short, so that halos leave early)
   uint64_t task_done;                      // u32 per task in local memory, only ever growing
   uint64_t push_up_ptr_odd, push_dn_ptr_odd;  // the push targets of odd passes (the other buffer)
   uint8_t lut1[256];

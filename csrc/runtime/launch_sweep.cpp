@@ -376,8 +376,20 @@ extern "C" int b2i_cuda_run_resident_fused(b2i_plan_t* plan, const b2i_launch_t*
     B2I_FAIL(B2I_ERR_UNSUPPORTED, "band buffers the tensor maps do not take");
   P.n_strips = (L.W + kS5Strip - 1) / kS5Strip;
   const int resident = sms * kS5CtasPerSm * kS5Warps;
-  P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kS5Chunk, 5, 120, 4);
-  P.n_segs = (y1 - y0 + P.seg_rows - 1) / P.seg_rows;
+  // With neighbours, the first and the last segment are one box (5 rows) high: those tasks run first
+  // and are short, so their halo rows and flags are under way while the other tasks still work, and
+  // the wait for the neighbour's rows of the pass before is over before it could hold anything up.
+  P.strip_flags = (L.flags & B2I_LAUNCH_STRIP_FLAGS) ? 1 : 0;
+  if (P.strip_flags && P.n_strips > B2I_MAX_STRIPS) B2I_FAIL(B2I_ERR_UNSUPPORTED, "image wider than the strip flags");
+  if (pushes && passes > 1 && y1 - y0 >= 4 * kS5Chunk && !env_int("B200IMG_NO_BSEG", 0)) {
+    P.bseg = kS5Chunk;
+    const int mid = y1 - y0 - 2 * P.bseg;
+    P.seg_rows = sweep_seg_rows(P.n_strips, mid, std::max(kS5Warps, resident - 2 * P.n_strips), kS5Chunk, 5, 120, 4);
+    P.n_segs = 2 + (mid + P.seg_rows - 1) / P.seg_rows;
+  } else {
+    P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kS5Chunk, 5, 120, 4);
+    P.n_segs = (y1 - y0 + P.seg_rows - 1) / P.seg_rows;
+  }
   P.n_tasks = P.n_strips * P.n_segs;
   if (P.n_tasks + 8 > n_task_flags)
     B2I_FAIL(B2I_ERR_ARG, "%d task flags given, %d needed", n_task_flags, P.n_tasks + 8);
@@ -389,6 +401,7 @@ extern "C" int b2i_cuda_run_resident_fused(b2i_plan_t* plan, const b2i_launch_t*
       P.push_dn_ptr_odd =
           odd->push_dn.ptr + (uint64_t)((int64_t)(y1 - L.push_rows - odd->push_dn.y_begin) * odd->push_dn.pitch);
   }
+  if (P.bseg) P.n_up_tasks = P.n_dn_tasks = P.n_strips;   // the short segments hold all the pushed rows
   if (passes == 1) {   // a single pass reads what the scatter left and nobody reads its halo
     P.wait_up_flag = P.wait_dn_flag = P.signal_up_flag = P.signal_dn_flag = 0;
     P.push_up_ptr = P.push_dn_ptr = 0;

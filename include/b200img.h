@@ -162,6 +162,11 @@ typedef struct b2i_view {
 #define B2I_LAUNCH_DST_MCAST 4 /* dst is an NVLS multicast address (b2i_mcast_ptr): result rows leave by
                                   plain stores from registers / shared memory, which the switch
                                   replicates into every GPU's copy; TMA stores are not used on it */
+#define B2I_LAUNCH_STRIP_FLAGS 8 /* b2i_cuda_run_resident_fused: wait_*_flag / signal_*_flag are arrays of one u32
+                                    per 240-pixel strip (B2I_MAX_STRIPS each) instead of one flag per side: a
+                                    boundary task waits for the three strips above / below it and releases its own,
+                                    so no pass-wide count stands between a pushed halo row and its reader */
+#define B2I_MAX_STRIPS 256
 
 /* One band launch: produce rows [y0, y1) of chain(image) into dst, reading src.
  * src must cover rows [y0-halo, y1+halo) clipped to the image (halo = b2i_plan_halo); when src

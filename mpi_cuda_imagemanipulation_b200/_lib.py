@@ -116,7 +116,7 @@ def has(symbol: str) -> bool:
 
 
 # ---- CUDA path (present once the kernels are linked in) ----------------------------------------
-LAUNCH_NO_TMA, LAUNCH_NAIVE, LAUNCH_DST_MCAST = 1, 2, 4
+LAUNCH_NO_TMA, LAUNCH_NAIVE, LAUNCH_DST_MCAST, LAUNCH_STRIP_FLAGS = 1, 2, 4, 8
 
 
 class View(C.Structure):

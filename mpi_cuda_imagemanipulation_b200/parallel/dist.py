@@ -28,6 +28,7 @@ from ..ops.chain import band_rows
 
 G = 8                     # ghost rows above/below a resident band (kGhostRows)
 W_COUNTERS, W_STATUS, W_FLAG_UP, W_FLAG_DN, W_DONE = 0, 16, 32, 36, 64   # byte offsets in `words`
+W_SF_UP, W_SF_DN = 1024, 2048   # per-strip flags (256 u32 each) written by the upper / lower neighbour
 
 
 class SymBuf:
@@ -274,7 +275,7 @@ class DistRuntime:
                                     self.stream()))
         self.barrier()
 
-    def _resident_launch(self, inb: int, halo: int, no_tma=False, plan=None) -> Launch:
+    def _resident_launch(self, inb: int, halo: int, no_tma=False, plan=None, strip_flags=False) -> Launch:
         g = self.rgeom
         outb = inb ^ 1
         L = Launch()
@@ -292,14 +293,14 @@ class DistRuntime:
             if up is not None:
                 uy0, uy1 = band_rows(g["H"], self.world, up)
                 L.push_up = View(self.band[outb].ptrs[up] + g["bp"] * (G + (uy1 - uy0)), g["bp"], self.y0, self.y0 + G)
-                L.wait_up_flag = self.words.local + W_FLAG_UP
-                L.signal_up_flag = self.words.ptrs[up] + W_FLAG_DN
+                L.wait_up_flag = self.words.local + (W_SF_UP if strip_flags else W_FLAG_UP)
+                L.signal_up_flag = self.words.ptrs[up] + (W_SF_DN if strip_flags else W_FLAG_DN)
             if dn is not None:
                 L.push_dn = View(self.band[outb].ptrs[dn] + g["bp"] * (G - halo), g["bp"], self.y1 - halo, self.y1)
-                L.wait_dn_flag = self.words.local + W_FLAG_DN
-                L.signal_dn_flag = self.words.ptrs[dn] + W_FLAG_UP
+                L.wait_dn_flag = self.words.local + (W_SF_DN if strip_flags else W_FLAG_DN)
+                L.signal_dn_flag = self.words.ptrs[dn] + (W_SF_UP if strip_flags else W_FLAG_UP)
         L.stream = self.stream()
-        L.flags = _lib.LAUNCH_NO_TMA if no_tma else 0
+        L.flags = (_lib.LAUNCH_NO_TMA if no_tma else 0) | (_lib.LAUNCH_STRIP_FLAGS if strip_flags else 0)
         return L
 
     N_TASK_FLAGS = 16384
@@ -318,7 +319,9 @@ class DistRuntime:
             if fused and not no_tma:
                 if getattr(self, "_task_flags", None) is None:
                     self._task_flags = torch.zeros(self.N_TASK_FLAGS, dtype=torch.int32, device=self.device)
-                rc = lib.b2i_cuda_run_resident_fused(plan.handle, C.byref(even), C.byref(odd), passes, self.epoch,
+                sf = not os.environ.get("B200IMG_NO_STRIP_FLAGS")
+                ev, od = self._resident_launch(0, halo, no_tma, plan, sf), self._resident_launch(1, halo, no_tma, plan, sf)
+                rc = lib.b2i_cuda_run_resident_fused(plan.handle, C.byref(ev), C.byref(od), passes, self.epoch,
                                                      self._task_flags.data_ptr(), self.N_TASK_FLAGS)
                 if rc != _lib.B2I_ERR_UNSUPPORTED:
                     check(rc)
@@ -350,6 +353,15 @@ def _timed(fn, stream_sync=True):
     return float(ms.item())
 
 
+def _config_block(W, H, n):
+    import importlib.util
+    root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    spec = importlib.util.spec_from_file_location("_b2i_bench_common", os.path.join(root, "bench_common.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.config_block(W, H, n)
+
+
 def _boundary_rows(H: int, bands, reach: int = 8):
     """Row ranges to verify: the top, the bottom and `reach` rows either side of every band boundary."""
     cuts = sorted({b[0] for b in bands if b[1] > b[0]} | {b[1] for b in bands if b[1] > b[0]})
@@ -367,6 +379,49 @@ def _check_rows(chain, img: np.ndarray, got: np.ndarray, spans) -> dict:
         bad += int((got[a:b].reshape(b - a, -1) != want.reshape(b - a, -1)).sum())
         rows += b - a
     return {"ok": bad == 0, "rows_checked": rows, "spans": len(spans), "mismatching_bytes": bad}
+
+
+def _resident_extra(rt, chain: str, W: int, H: int, img, checked: dict, key: str, p_check: int, p_time: int,
+                    reuse_root: bool = False) -> dict:
+    """Resident bands of a WxH image: p_check passes checked bit for bit around every band boundary
+    (gathered to the root), then p_time passes per timed call: one cooperative launch that walks the
+    passes where the chain allows it, and one launch per pass for comparison. Collective."""
+    import mpi_cuda_imagemanipulation_b200 as b2
+    from ..ops.cuda import Plan
+    rank, world = rt.rank, rt.world
+    try:
+        plan = Plan(chain, 3)
+        if not reuse_root:
+            img = b2.synth_image(W, H, 3, seed=2) if rank == 0 else None
+            rt.setup_root(W, H, 3, 3)
+            rt.load_root(img)
+        rt.setup_resident(W, H, 3)
+        rt.scatter_resident(rt.src.ptrs[0], rt.geom["sp"])
+        fused_ran = rt.run_resident(plan, p_check)
+        rt.barrier()
+        rt.gather_resident(p_check, rt.dst.ptrs[0], rt.geom["dp"], 3)
+        got = rt.fetch_root()
+        ok = True
+        if rank == 0:
+            bands = [band_rows(H, world, r) for r in range(world)]
+            checked[key] = _check_rows(",".join([chain] * p_check), img, got, _boundary_rows(H, bands))
+            checked[key]["fused_launch"] = bool(fused_ran)
+            ok = checked[key]["ok"]
+        del got
+        out = {"passes_per_call": p_time, "halo_rows": plan.halo, "image": f"{W}x{H}", "chain": chain}
+        for mode in (("fused", "per_pass_launches") if fused_ran else ("per_pass_launches",)):
+            rt.scatter_resident(rt.src.ptrs[0], rt.geom["sp"])
+            rt.run_resident(plan, p_time, fused=mode == "fused")
+            rt.barrier()
+            rr = [_timed(lambda: rt.run_resident(plan, p_time, fused=mode == "fused")) / p_time for _ in range(5)]
+            out[mode + "_ms_per_pass"] = round(statistics.median(rr), 5)
+        best = min(v for k, v in out.items() if k.endswith("_ms_per_pass"))
+        out.update(ms_per_pass=best, mpix_per_s=round(W * H / 1e6 / (best / 1e3), 1), status=rt.status(), checked_ok=ok)
+        if rank == 0 and not ok:
+            out["error"] = f"result mismatch: {checked[key]}"
+        return out
+    except Exception as e:  # extras must not take the headline down
+        return {"error": f"{type(e).__name__}: {e}"[:200]}
 
 
 def bench_distributed(args, rank: int, world: int, local: int) -> Optional[dict]:
@@ -480,35 +535,13 @@ def bench_distributed(args, rank: int, world: int, local: int) -> Optional[dict]
         checked["e2e_every_rank"] = _check_rows(chain, img, h_out.reshape(H, W, 3), spans)
         assert checked["e2e_every_rank"]["ok"], f"e2e output mismatch: {checked['e2e_every_rank']}"
 
-    # ---- extra: resident 5x5 Gaussian passes with fused halo push (BASELINE.json config 3) ------------
+    # ---- extras: resident bands, halo rows pushed from inside the kernels (BASELINE.json configs 3 and 4) ----
     extras = {}
-    try:
-        gplan = Plan("gauss5", 3)
-        rt.setup_resident(W, H, 3)
-        rt.scatter_resident(rt.src.ptrs[0], rt.geom["sp"])
-        P = 8
-        rt.run_resident(gplan, P)
-        rt.barrier()
-        # what P resident passes (halo rows pushed between GPUs every pass) produced, gathered and
-        # compared with P host blurs around every band boundary; timing follows on the same buffers
-        rt.gather_resident(P, rt.dst.ptrs[0], rt.geom["dp"], 3)
-        got_r = rt.fetch_root()
-        if rank == 0:
-            rbands = [band_rows(H, world, r) for r in range(world)]
-            checked["gauss5_resident"] = _check_rows(",".join(["gauss5"] * P), img, got_r, _boundary_rows(H, rbands))
-        rt.scatter_resident(rt.src.ptrs[0], rt.geom["sp"])
-        rr = []
-        for _ in range(5):
-            rr.append(_timed(lambda: rt.run_resident(gplan, P)) / P)
-            if os.environ.get("B200IMG_BENCH_DEBUG"):
-                print(f"[rank {rank}] resident call: {rr[-1]:.4f} ms/pass status={rt.status()} epoch={rt.epoch}", flush=True)
-        rms = statistics.median(rr)
-        if rank == 0 and not checked.get("gauss5_resident", {}).get("ok", False):
-            raise RuntimeError(f"resident result mismatch: {checked.get('gauss5_resident')}")
-        extras["gauss5_resident"] = {"ms_per_pass": round(rms, 5), "mpix_per_s": round(W * H / 1e6 / (rms / 1e3), 1),
-                                     "passes": P, "halo_rows": 2, "status": rt.status()}
-    except Exception as e:  # extras must not take the headline down
-        extras["gauss5_resident"] = {"error": f"{type(e).__name__}: {e}"[:200]}
+    extras["gauss5_resident"] = _resident_extra(rt, "gauss5", W, H, img, checked, "gauss5_resident",
+                                                p_check=8, p_time=64, reuse_root=True)
+    if os.environ.get("B200IMG_BENCH_CONFIG4", "1") != "0":
+        extras["blur_sobel_16k_resident"] = _resident_extra(rt, "gauss5,sobel", 16384, 16384, None, checked,
+                                                            "blur_sobel_16k_resident", p_check=2, p_time=8)
 
     mp = W * H / 1e6
     res = None
@@ -518,9 +551,8 @@ def bench_distributed(args, rank: int, world: int, local: int) -> Optional[dict]
             "value": round(mp / (ms / 1e3), 1), "unit": "MP/s", "n_gpus": world, "steps": K, "warmup": Wm,
             "ms_per_step": round(ms, 6), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "uint8", "data": "synthetic",
-            "config": {"model": "kernel_cu pipeline: gray->contrast3.5->emboss3x3->BGR (kernel.cu:192-210)",
-                       "image": f"{W}x{H} RGB", "global_batch": 1, "seq_len": W * H, "parallelism": f"bands{world}",
-                       "mode": "root-owned input and output on GPU 0; scatter and gather fused into the filter "
+            "config": _config_block(W, H, world),
+            "detail": {"mode": "root-owned input and output on GPU 0; scatter and gather fused into the filter "
                                "kernel over NVLink peer memory (IPC), done flags acquired on the root each step",
                        "bands": f"root GPU takes {share:.3f} of the rows, the other {world - 1} split the rest: the share is "
                                 f"the fastest of the link model's (root's local rate vs the others' combined rate through "
