@@ -25,9 +25,11 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t by
                : "memory");
 }
 // Waits for the phase with the given parity. A TMA transfer that never completes (bad tensor
-// map, faulting peer) would otherwise spin forever and hang the GPU: after ~4 s the kernel traps,
-// which surfaces as a launch failure on the host.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+// map, faulting peer) would otherwise spin forever and hang the GPU. After ~4 s the wait gives up:
+// with a status word (multi-GPU launches pass theirs) it records code 5 there and the thread leaves
+// the kernel, so the launch ends and the context stays usable; without one it traps, which surfaces
+// as a launch failure on the host.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32_t* status = nullptr) {
   const uint32_t addr = smem_u32(bar);
   unsigned long long t0 = 0;
   for (uint32_t spins = 0;; ++spins) {
@@ -44,7 +46,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       unsigned long long t;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
       if (t0 == 0) t0 = t;
-      else if (t - t0 > 4000000000ull) __trap();
+      else if (t - t0 > 4000000000ull) {
+        if (!status) __trap();
+        atomicExch(status, 5u);
+        asm volatile("exit;");
+      }
     }
   }
 }
@@ -115,15 +121,25 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-// Spins until *p >= want (epochs only grow). Gives up after `timeout_ns` so that a lost peer
-// shows up as an error code instead of a hung GPU; returns false on timeout.
-__device__ __forceinline__ bool wait_flag_ge(const uint32_t* p, uint32_t want,
-                                             unsigned long long timeout_ns) {
-  if ((int32_t)(ld_acquire_sys(p) - want) >= 0) return true;
+// A flag that is kAbortBias or more ahead of any epoch asked for is poison: its writer gave up
+// (timed out itself, or saw poison) and says so to whoever waits on it, so that one lost GPU ends
+// every GPU's kernel within one timeout instead of one timeout per neighbour in a row.
+constexpr uint32_t kAbortBias = 1u << 30;
+__device__ __forceinline__ void flag_poison(uint32_t* p, uint32_t epoch) { st_release_sys(p, epoch + kAbortBias); }
+// Spins until *p >= want (epochs only grow). Gives up after `timeout_ns`, when the flag is poison,
+// or when this GPU's status word (if given) is already nonzero, so that a lost peer shows up as an
+// error code instead of a hung GPU (the reference's peers hang, kernel.cu:111-114,127).
+// Returns false when it gave up.
+__device__ __forceinline__ bool wait_flag_ge(const uint32_t* p, uint32_t want, unsigned long long timeout_ns,
+                                             const uint32_t* status = nullptr) {
+  uint32_t d = ld_acquire_sys(p) - want;
+  if ((int32_t)d >= 0) return d < (kAbortBias >> 1);
   unsigned long long t0;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
   for (;;) {
-    if ((int32_t)(ld_acquire_sys(p) - want) >= 0) return true;
+    d = ld_acquire_sys(p) - want;
+    if ((int32_t)d >= 0) return d < (kAbortBias >> 1);
+    if (status && *reinterpret_cast<const volatile uint32_t*>(status) != 0) return false;
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     if (t - t0 > timeout_ns) return false;
@@ -141,12 +157,14 @@ __device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ bool wait_flag_ge_gpu(const uint32_t* p, uint32_t want, unsigned long long timeout_ns) {
+__device__ __forceinline__ bool wait_flag_ge_gpu(const uint32_t* p, uint32_t want, unsigned long long timeout_ns,
+                                                 const uint32_t* status = nullptr) {
   if ((int32_t)(ld_acquire_gpu(p) - want) >= 0) return true;
   unsigned long long t0;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
   for (;;) {
     if ((int32_t)(ld_acquire_gpu(p) - want) >= 0) return true;
+    if (status && *reinterpret_cast<const volatile uint32_t*>(status) != 0) return false;
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     if (t - t0 > timeout_ns) return false;

@@ -113,7 +113,6 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
   uint8_t* in_ring = smem + warp * P.warp_smem;        // NST stages of CH rows x kSweepInBytes (128 B aligned)
   uint8_t* out_ring = in_ring + NST * P.in_stage_bytes;  // 2 staging buffers of CH rows x out_pitch
   uint64_t* bar = &bars[warp * NST];
-  uint8_t* dummy = out_ring + 2 * P.out_buf_bytes + (lane == 0 ? 0 : 32);  // 64 spare bytes per warp
   const bool halo_lane = lane == 0 || lane == 31;
   const GrayRefCoef gk = gray_ref_coef(P.rgb_order);
   const int rgb = P.rgb_order;
@@ -262,9 +261,11 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
           r0 = lut4s(lut1, r0);
           r1 = lut4s(lut1, r1);
         }
-        {
-          // halo lanes (0, 31) store into a per-warp dummy slot: no divergent branch around the stores
-          uint8_t* d = halo_lane ? dummy : out_ring + ob * P.out_buf_bytes + er * out_pitch + (lane - 1) * (expand ? 24 : 8);
+        if (!halo_lane) {
+          // predicated stores: the halo lanes (0, 31) stage nothing. (They used to store into a spare
+          // slot; that slot sat on the banks of two other lanes and made every staging store a 3- or
+          // 4-way bank conflict: ncu, profiles/ncu/prof_r2_sweep3_kernel_cu.json.)
+          uint8_t* d = out_ring + ob * P.out_buf_bytes + er * out_pitch + (lane - 1) * (expand ? 24 : 8);
           if (expand) {  // kernel.cu:210 in registers: 8 gray -> 24 bytes
             uint2* qd = reinterpret_cast<uint2*>(d);
             qd[0] = make_uint2(__byte_perm(r0, 0, 0x1000), __byte_perm(r0, 0, 0x2211));

@@ -112,7 +112,6 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
   uint8_t* in_ring = smem + warp * P.warp_smem;          // NST stages of CH rows x kS5InBytes
   uint8_t* out_ring = in_ring + NST * P.in_stage_bytes;  // 2 staging buffers of CH rows x kS5OutBytes
   uint64_t* bar = &bars[warp * NST];
-  uint8_t* dummy = out_ring + 2 * P.out_buf_bytes + (lane == 0 ? 0 : 32);  // halo lanes store here
   const bool halo_lane = lane == 0 || lane == 31;
   int wh[5], wv[5];
 #pragma unroll
@@ -164,8 +163,8 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
         if (s2 >= 0 && s2 < P.n_strips && g2 >= 0 && g2 < P.n_segs) {
           const int so2 = g2 == 0 ? 0 : g2 == P.n_segs - 1 ? 1 : g2 + 1;
           if (!wait_flag_ge_gpu(reinterpret_cast<const uint32_t*>(P.task_done) + so2 * P.n_strips + s2,
-                                P.wait_epoch + (uint32_t)pass, P.timeout_ns))
-            atomicExch(reinterpret_cast<uint32_t*>(P.status), 4u);
+                                P.wait_epoch + (uint32_t)pass, P.timeout_ns, reinterpret_cast<const uint32_t*>(P.status)))
+            atomicCAS(reinterpret_cast<uint32_t*>(P.status), 0u, 4u);
         }
       }
       __syncwarp();
@@ -179,8 +178,9 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
         const uint64_t base = up ? P.wait_up_flag : P.wait_dn_flag;
         const bool need = up ? (ya - 2 < P.y0 || sig_up) : (yb + 2 > P.y1 || sig_dn);
         if (base && need && s2 >= 0 && s2 < P.n_strips &&
-            !wait_flag_ge(reinterpret_cast<const uint32_t*>(base) + s2, P.wait_epoch + (uint32_t)pass, P.timeout_ns))
-          atomicExch(reinterpret_cast<uint32_t*>(P.status), up ? 1u : 2u);
+            !wait_flag_ge(reinterpret_cast<const uint32_t*>(base) + s2, P.wait_epoch + (uint32_t)pass, P.timeout_ns,
+                          reinterpret_cast<const uint32_t*>(P.status)))
+          sweep_abort(P, up ? 1u : 2u, P.signal_epoch + (uint32_t)pass, P.n_strips);
       }
       __syncwarp();
       if (lane == 0) asm volatile("fence.proxy.async;" ::: "memory");
@@ -297,9 +297,8 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
 #pragma unroll
           for (int m = 0; m < 6; ++m) r[m] = lut4q(lut1, r[m]);
         }
-        {
-          uint2* d = reinterpret_cast<uint2*>(halo_lane ? dummy
-                                                        : out_ring + ob * P.out_buf_bytes + er * kS5OutBytes + (lane - 1) * 24);
+        if (!halo_lane) {   // predicated: the halo lanes stage nothing (a spare slot for them cost bank conflicts)
+          uint2* d = reinterpret_cast<uint2*>(out_ring + ob * P.out_buf_bytes + er * kS5OutBytes + (lane - 1) * 24);
           d[0] = make_uint2(r[0], r[1]);
           d[1] = make_uint2(r[2], r[3]);
           d[2] = make_uint2(r[4], r[5]);
@@ -333,7 +332,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
       // output box c-1 is finished during rows 0..3 of input box c; box c starts at row 4
       const uint32_t ob_prev = (n_out + c + 1) & 1, ob_cur = (n_out + c) & 1;
       const int rows_here = min(CH, steps - c * CH);
-      mbar_wait(&bar[st], ((n_in + c) / NST) & 1);
+      mbar_wait(&bar[st], ((n_in + c) / NST) & 1, MG ? reinterpret_cast<uint32_t*>(P.status) : nullptr);
       step(std::integral_constant<int, 0>{}, slowc, c, stage_base, ob_prev, ob_cur, X2, X1, X0, X4, X3);
       if (rows_here > 1) step(std::integral_constant<int, 1>{}, slowc, c, stage_base, ob_prev, ob_cur, X3, X2, X1, X0, X4);
       if (rows_here > 2) step(std::integral_constant<int, 2>{}, slowc, c, stage_base, ob_prev, ob_cur, X4, X3, X2, X1, X0);

@@ -12,17 +12,29 @@ namespace dev {
 // first sees the neighbour's flag of the previous pass: its rows have landed here and it has
 // finished reading what this task overwrites. `reach` = rows of halo the stencil reads beyond the
 // task's own rows.
+// This GPU gives up (a wait timed out, or a neighbour's flag was poison): record why, and poison the
+// flags this launch would have released, so that the neighbours stop waiting too.
+template <class Params>
+__device__ __forceinline__ void sweep_abort(const Params& P, uint32_t code, uint32_t epoch, int n_flags = 1) {
+  atomicExch(reinterpret_cast<uint32_t*>(P.status), code);
+  for (int i = 0; i < n_flags; ++i) {
+    if (P.signal_up_flag) flag_poison(reinterpret_cast<uint32_t*>(P.signal_up_flag) + i, epoch);
+    if (P.signal_dn_flag) flag_poison(reinterpret_cast<uint32_t*>(P.signal_dn_flag) + i, epoch);
+  }
+}
+
 template <class Params>
 __device__ __forceinline__ void sweep_wait_neighbours(const Params& P, int ya, int yb, int reach, bool sig_up,
                                                       bool sig_dn, uint32_t pass = 0) {
+  const uint32_t* st = reinterpret_cast<const uint32_t*>(P.status);
   if (P.wait_up_flag && (ya - reach < P.y0 || sig_up)) {
-    if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_up_flag), P.wait_epoch + pass, P.timeout_ns))
-      atomicExch(reinterpret_cast<uint32_t*>(P.status), 1u);
+    if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_up_flag), P.wait_epoch + pass, P.timeout_ns, st))
+      sweep_abort(P, 1u, P.signal_epoch + pass);
     asm volatile("fence.proxy.async;" ::: "memory");  // the flag (generic proxy) before TMA loads of the ghost rows
   }
   if (P.wait_dn_flag && (yb + reach > P.y1 || sig_dn)) {
-    if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_dn_flag), P.wait_epoch + pass, P.timeout_ns))
-      atomicExch(reinterpret_cast<uint32_t*>(P.status), 2u);
+    if (!wait_flag_ge(reinterpret_cast<const uint32_t*>(P.wait_dn_flag), P.wait_epoch + pass, P.timeout_ns, st))
+      sweep_abort(P, 2u, P.signal_epoch + pass);
     asm volatile("fence.proxy.async;" ::: "memory");
   }
 }

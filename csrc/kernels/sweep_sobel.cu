@@ -74,7 +74,6 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
   uint8_t* in_ring = smem + warp * P.warp_smem;          // NST stages of CH rows x kSSInBytes
   uint8_t* out_ring = in_ring + NST * P.in_stage_bytes;  // 2 staging buffers of CH rows x kSSOutBytes
   uint64_t* bar = &bars[warp * NST];
-  uint8_t* dummy = out_ring + 2 * P.out_buf_bytes + (lane == 0 ? 0 : 32);  // halo lanes store here
   const bool halo_lane = lane == 0 || lane == 31;
   const bool reflect = P.border == B2I_BORDER_REFLECT101, replicate = P.border == B2I_BORDER_REPLICATE;
 
@@ -194,9 +193,8 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
 #pragma unroll
           for (int m = 0; m < 6; ++m) r[m] = lut4s(lut1, r[m]);
         }
-        {
-          uint2* d = reinterpret_cast<uint2*>(halo_lane ? dummy
-                                                        : out_ring + ob * P.out_buf_bytes + er * kSSOutBytes + (lane - 1) * 24);
+        if (!halo_lane) {   // predicated: the halo lanes stage nothing (a spare slot for them cost bank conflicts)
+          uint2* d = reinterpret_cast<uint2*>(out_ring + ob * P.out_buf_bytes + er * kSSOutBytes + (lane - 1) * 24);
           d[0] = make_uint2(r[0], r[1]);
           d[1] = make_uint2(r[2], r[3]);
           d[2] = make_uint2(r[4], r[5]);

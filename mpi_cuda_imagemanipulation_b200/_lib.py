@@ -19,6 +19,7 @@ LIB_PATH = os.environ.get("B200IMG_LIB") or os.path.join(_HERE, "lib", "libb200i
 B2I_MAX_OPS = 16
 B2I_MAX_GPUS = 16
 B2I_ERR_UNSUPPORTED = -4
+B2I_ERR_TIMEOUT = -6
 
 # b2i_status
 OK, ERR_ARG, ERR_IO, ERR_CUDA, ERR_UNSUPPORTED, ERR_NO_DEVICE, ERR_TIMEOUT, ERR_NOMEM = (

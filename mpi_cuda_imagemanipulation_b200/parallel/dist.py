@@ -56,6 +56,7 @@ class DistRuntime:
         self._shm = []
         self.words = self.symmetric(4096)
         self.epoch = 0
+        self.timeout_ns = 0       # device-side waits give up after this long (0 = 2 s)
         self.geom = None
 
     # ---- plumbing ---------------------------------------------------------------------------------
@@ -127,6 +128,35 @@ class DistRuntime:
         torch.cuda.synchronize()
         return int(st.item())
 
+    def check_status(self) -> None:
+        """Collective. Device-side waits never hang: a wait that times out (or meets a flag its writer
+        poisoned when it gave up) records a code in this rank's status word and the kernel carries on to
+        its end. Here every rank learns whether ANY rank recorded one: if so the flags, epochs and the
+        status words are reset on every rank, so the runtime stays usable, and every rank raises
+        ``B200ImgError`` with ``B2I_ERR_TIMEOUT``. (The reference's ranks hang in ``MPI_Barrier`` when
+        one of them fails, ``kernel.cu:111-114,127``.)"""
+        st = self.status()
+        t = torch.tensor([st], device=self.device, dtype=torch.int32)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        worst = int(t.item())
+        if worst == 0:
+            return
+        self.reset_flags()
+        raise _lib.B200ImgError(_lib.B2I_ERR_TIMEOUT,
+                                f"a device-side wait gave up (this rank's status {st}, worst over ranks {worst}): "
+                                f"1/2 = upper/lower neighbour's halo flag, 3 = a done flag, 4 = a task flag, 5 = a TMA load")
+
+    def reset_flags(self) -> None:
+        """Collective: zeroes every rank's flag words and task flags and restarts the epochs."""
+        self.barrier()
+        z = torch.zeros(self.words.nbytes, dtype=torch.uint8, device=self.device)
+        check(lib.b2i_cuda_memcpy2d(self.words.local, self.words.nbytes, z.data_ptr(), self.words.nbytes,
+                                    self.words.nbytes, 1, 2, self.stream()))
+        if getattr(self, "_task_flags", None) is not None:
+            self._task_flags.zero_()
+        self.epoch = 0
+        self.barrier()
+
     # ---- ROOT mode: root-owned device images, scatter/gather fused into the kernels ------------------
     def setup_root(self, W: int, H: int, Cn: int, out_c: int):
         sp, dp = (W * Cn + 15) // 16 * 16, (W * out_c + 15) // 16 * 16
@@ -195,6 +225,7 @@ class DistRuntime:
         L.counters = self.words.local + W_COUNTERS
         L.status = self.words.local + W_STATUS
         L.stream = self.stream()
+        L.timeout_ns = self.timeout_ns
         L.flags = _lib.LAUNCH_NO_TMA if no_tma else 0
         return L
 
@@ -300,6 +331,7 @@ class DistRuntime:
                 L.wait_dn_flag = self.words.local + (W_SF_DN if strip_flags else W_FLAG_DN)
                 L.signal_dn_flag = self.words.ptrs[dn] + (W_SF_UP if strip_flags else W_FLAG_UP)
         L.stream = self.stream()
+        L.timeout_ns = self.timeout_ns
         L.flags = (_lib.LAUNCH_NO_TMA if no_tma else 0) | (_lib.LAUNCH_STRIP_FLAGS if strip_flags else 0)
         return L
 

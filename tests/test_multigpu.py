@@ -24,6 +24,18 @@ def test_torchrun_ranks_match_host_reference(n):
     assert "DIST_CHECK PASS" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
 
 
+@pytest.mark.parametrize("n", [2, 4])
+def test_lost_peer_is_a_timeout_error_not_a_hang(n):
+    """One rank never joins a resident run: every rank gets B2I_ERR_TIMEOUT within the (50 ms) timeout
+    and the runtime works again afterwards (scripts/dist_fault.py)."""
+    if torch.cuda.device_count() < n:
+        pytest.skip(f"needs {n} GPUs")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+                        "--master-addr", "127.0.0.1", "--master-port", str(29520 + n),
+                        os.path.join(ROOT, "scripts", "dist_fault.py")], capture_output=True, text=True, timeout=600)
+    assert "DIST_FAULT PASS" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
 def test_in_process_runtime_on_real_peers():
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
