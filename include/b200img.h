@@ -136,6 +136,20 @@ int b2i_host_run_ranks(const b2i_chain_t* chain, const uint8_t* src, int W, int 
 int b2i_read_pnm(const char* path, int order, uint8_t** data, int* W, int* H, int* C);
 int b2i_write_pnm(const char* path, int order, const uint8_t* data, int W, int H, int C,
                   size_t pitch);
+/* JPEG, the reference's own file format (cv::imread / cv::imwrite on rank 0: kernel.cu:110,236;
+ * kern.cpp:33,92), through nvJPEG on the current CUDA device (csrc/core/jpeg.cpp; the library is
+ * loaded on first use, B2I_ERR_UNSUPPORTED without it). A grayscale file reads as 1 channel, like
+ * IMREAD_UNCHANGED. Writing is baseline 4:4:4 at `quality` (1..100, 0 = 95): lossy, so results
+ * read back close to, not equal to, what was written. File I/O is outside every timed region. */
+int b2i_jpeg_available(void);
+int b2i_read_jpeg(const char* path, int order, uint8_t** data, int* W, int* H, int* C);
+int b2i_write_jpeg(const char* path, int order, const uint8_t* data, int W, int H, int C, size_t pitch,
+                   int quality);
+/* Any supported file: JPEG by content, else PPM / PGM; writing picks the format by extension
+ * (.jpg / .jpeg -> JPEG, anything else -> PPM / PGM). */
+int b2i_read_image(const char* path, int order, uint8_t** data, int* W, int* H, int* C);
+int b2i_write_image(const char* path, int order, const uint8_t* data, int W, int H, int C, size_t pitch,
+                    int quality);
 /* Headerless interleaved bytes, exactly the reference's scatter payload (kernel.cu:135-137). */
 int b2i_read_raw(const char* path, int W, int H, int C, uint8_t** data);
 int b2i_write_raw(const char* path, const uint8_t* data, int W, int H, int C, size_t pitch);

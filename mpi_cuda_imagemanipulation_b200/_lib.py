@@ -106,6 +106,9 @@ _sig("b2i_host_run_ranks", C.c_int, _P(ChainStruct), u8p, C.c_int, C.c_int, C.c_
 _sig("b2i_read_pnm", C.c_int, C.c_char_p, C.c_int, _P(C.c_void_p), _P(C.c_int), _P(C.c_int),
      _P(C.c_int))
 _sig("b2i_write_pnm", C.c_int, C.c_char_p, C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_size_t)
+_sig("b2i_jpeg_available", C.c_int)
+_sig("b2i_read_image", C.c_int, C.c_char_p, C.c_int, _P(C.c_void_p), _P(C.c_int), _P(C.c_int), _P(C.c_int))
+_sig("b2i_write_image", C.c_int, C.c_char_p, C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_int)
 _sig("b2i_read_raw", C.c_int, C.c_char_p, C.c_int, C.c_int, C.c_int, _P(C.c_void_p))
 _sig("b2i_write_raw", C.c_int, C.c_char_p, u8p, C.c_int, C.c_int, C.c_int, C.c_size_t)
 _sig("b2i_free", None, C.c_void_p)

@@ -1,7 +1,7 @@
-"""PPM / PGM / raw file I/O and synthetic images (``csrc/core/io.cpp``).
+"""JPEG / PPM / PGM / raw file I/O and synthetic images (``csrc/core/io.cpp``, ``csrc/core/jpeg.cpp``).
 
-The reference's file I/O is ``cv::imread`` / ``cv::imwrite`` of JPEG on rank 0 (``kernel.cu:110,236``);
-here the same interleaved bytes are kept lossless.
+The reference's file I/O is ``cv::imread`` / ``cv::imwrite`` of JPEG on rank 0 (``kernel.cu:110,236``):
+JPEG files go through nvJPEG (needs a GPU); PPM / PGM / raw keep the same interleaved bytes lossless.
 """
 from __future__ import annotations
 
@@ -14,10 +14,10 @@ from .._lib import check, lib
 
 
 def read_image(path: str, order: str = "bgr") -> np.ndarray:
-    """Reads a binary PPM/PGM into an HxWxC uint8 array (3-channel data in ``order``)."""
+    """Reads a JPEG (by content) or a binary PPM/PGM into an HxWxC uint8 array (3-channel data in ``order``)."""
     data = C.c_void_p()
     W, H, Cn = C.c_int(), C.c_int(), C.c_int()
-    check(lib.b2i_read_pnm(path.encode(), _lib.ORDERS[order], C.byref(data), C.byref(W),
+    check(lib.b2i_read_image(path.encode(), _lib.ORDERS[order], C.byref(data), C.byref(W),
                            C.byref(H), C.byref(Cn)))
     try:
         n = W.value * H.value * Cn.value
@@ -27,12 +27,13 @@ def read_image(path: str, order: str = "bgr") -> np.ndarray:
     return arr.reshape(H.value, W.value, Cn.value)
 
 
-def write_image(path: str, img, order: str = "bgr") -> None:
+def write_image(path: str, img, order: str = "bgr", quality: int = 95) -> None:
+    """``.jpg`` / ``.jpeg``: JPEG at ``quality`` (lossy; nvJPEG, needs a GPU); anything else: binary PPM / PGM."""
     a = np.ascontiguousarray(np.asarray(img), dtype=np.uint8)
     if a.ndim == 2:
         a = a[:, :, None]
     H, W, Cn = a.shape
-    check(lib.b2i_write_pnm(path.encode(), _lib.ORDERS[order], a.ctypes.data, W, H, Cn, W * Cn))
+    check(lib.b2i_write_image(path.encode(), _lib.ORDERS[order], a.ctypes.data, W, H, Cn, W * Cn, quality))
 
 
 def read_raw(path: str, W: int, H: int, Cn: int = 3) -> np.ndarray:
