@@ -481,7 +481,7 @@ extern "C" int b2i_ctx_run_resident(b2i_ctx* c, b2i_plan_t* plan, int passes, in
   }
   const uint32_t epoch0 = c->epoch;
   // one (device, pass) launch
-  auto launch_pass = [&](int i, int p) -> int {
+  auto launch_pass = [&](int i, int p, b2i_plan_t* plan) -> int {
     const int in = p & 1, outb = in ^ 1;
     Dev& d = c->devs[i];
     if (d.y1 == d.y0) return B2I_OK;
@@ -545,10 +545,13 @@ extern "C" int b2i_ctx_run_resident(b2i_ctx* c, b2i_plan_t* plan, int passes, in
     std::vector<std::string> errs(c->n);
     for (int i = 0; i < c->n; ++i)
       workers.emplace_back([&, i] {
+        b2i_plan_t* mine = nullptr;   // the plan records its last launch: one copy per launching thread
+        rcs[i] = b2i_plan_clone(plan, &mine);
         for (int p = 0; p < passes && rcs[i] == B2I_OK; ++p) {
-          rcs[i] = launch_pass(i, p);
+          rcs[i] = launch_pass(i, p, mine);
           if (rcs[i] != B2I_OK) errs[i] = b2i_last_error();
         }
+        if (mine) b2i_plan_destroy(mine);
       });
     for (auto& w : workers) w.join();
     for (int i = 0; i < c->n; ++i)
@@ -558,7 +561,7 @@ extern "C" int b2i_ctx_run_resident(b2i_ctx* c, b2i_plan_t* plan, int passes, in
       }
   } else {
     for (int p = 0; p < passes; ++p)
-      for (int i = 0; i < c->n; ++i) B2I_TRY(launch_pass(i, p));
+      for (int i = 0; i < c->n; ++i) B2I_TRY(launch_pass(i, p, plan));
   }
   c->epoch = epoch0 + passes + 1;
   // gather: each GPU copies its rows of the last output buffer into the root image

@@ -14,7 +14,7 @@ namespace b2i {
 int try_stencil_mma(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
                     const b2i_view_t& src, const b2i_view_t& dst, int sms, bool first, bool last) {
   (void)first;
-  if (!seg.mma_ok || env_int("B200IMG_NO_MMA", 0) || (L.flags & B2I_LAUNCH_NO_TMA) || env_int("B200IMG_NO_TMA", 0))
+  if (!seg.mma_ok || B2I_ENV("B200IMG_NO_MMA", 0) || (L.flags & B2I_LAUNCH_NO_TMA) || B2I_ENV("B200IMG_NO_TMA", 0))
     return 0;
   // multi-GPU hooks are not in this kernel (yet): the sweeps carry them
   if (L.push_rows || L.wait_up_flag || L.wait_dn_flag || L.signal_up_flag || L.signal_dn_flag ||
@@ -46,7 +46,7 @@ int try_stencil_mma(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, i
   P.fast8 = P.mode == SM_LINEAR && P.shift == 8 && nonneg && sum == 256 && P.bias >= 0 && P.bias < 256;
   P.n_bands = (y1 - y0 + kSmRows - 1) / kSmRows;
   P.n_slabs = (int)((W3 + kSmSlab - 1) / kSmSlab);
-  P.dbg = env_int("B200IMG_MMA_DBG", 0);
+  P.dbg = B2I_ENV("B200IMG_MMA_DBG", 0);
   if (const char* dp = getenv("B200IMG_MMA_DBGPTR")) P.dbg_ptr = strtoull(dp, nullptr, 0);
   CUtensorMap src_map, dst_map;
   const int src_rows = std::min(src.y_end, L.H) - src.y_begin;

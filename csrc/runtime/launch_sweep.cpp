@@ -29,8 +29,8 @@ static int sweep_seg_rows(int n_strips, int rows, int resident, int chunk, int l
 // 0 if the segment or the buffers do not qualify (the tile-chain kernel then runs it).
 int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
               const b2i_view_t& src, const b2i_view_t& dst, int sms, bool last) {
-  if (seg.phases.size() != 2 || env_int("B200IMG_NO_SWEEP", 0) || (L.flags & B2I_LAUNCH_NO_TMA) ||
-      env_int("B200IMG_NO_TMA", 0))
+  if (seg.phases.size() != 2 || B2I_ENV("B200IMG_NO_SWEEP", 0) || (L.flags & B2I_LAUNCH_NO_TMA) ||
+      B2I_ENV("B200IMG_NO_TMA", 0))
     return 0;
   const PhaseDesc& g = seg.phases[0];
   const PhaseDesc& st = seg.phases[1];
@@ -56,7 +56,7 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
   P.has_lut1 = st.lut >= 0;
   if (g.lut >= 0) memcpy(P.lut0, seg.luts[g.lut], 256);
   if (st.lut >= 0) memcpy(P.lut1, seg.luts[st.lut], 256);
-  if (g.lut >= 0 && seg.lut0_affine && !env_int("B200IMG_NO_AFFINE_LUT", 0)) {
+  if (g.lut >= 0 && seg.lut0_affine && !B2I_ENV("B200IMG_NO_AFFINE_LUT", 0)) {
     P.has_lut0 = 2;
     P.lut0_a = seg.aff_a;
     P.lut0_b = seg.aff_b;
@@ -180,8 +180,8 @@ static int sweep_seg_rows(int n_strips, int rows, int resident, int chunk, int l
 // segment or the buffers do not qualify, -1 on a launch error.
 int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
                const b2i_view_t& src, const b2i_view_t& dst, int sms, bool first, bool last) {
-  if (seg.phases.size() != 2 || env_int("B200IMG_NO_SWEEP", 0) || env_int("B200IMG_NO_SWEEP5", 0) ||
-      (L.flags & B2I_LAUNCH_NO_TMA) || env_int("B200IMG_NO_TMA", 0))
+  if (seg.phases.size() != 2 || B2I_ENV("B200IMG_NO_SWEEP", 0) || B2I_ENV("B200IMG_NO_SWEEP5", 0) ||
+      (L.flags & B2I_LAUNCH_NO_TMA) || B2I_ENV("B200IMG_NO_TMA", 0))
     return 0;
   const PhaseDesc& ph = seg.phases[0];
   const PhaseDesc& pv = seg.phases[1];
@@ -253,8 +253,8 @@ int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0
 // magnitude on 3-channel data (+LUT). Same return values as try_sweep5.
 int try_sweep_sobel(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0, int y1,
                     const b2i_view_t& src, const b2i_view_t& dst, int sms, bool first, bool last) {
-  if (seg.phases.size() != 1 || env_int("B200IMG_NO_SWEEP", 0) || env_int("B200IMG_NO_SWEEP_SOBEL", 0) ||
-      (L.flags & B2I_LAUNCH_NO_TMA) || env_int("B200IMG_NO_TMA", 0))
+  if (seg.phases.size() != 1 || B2I_ENV("B200IMG_NO_SWEEP", 0) || B2I_ENV("B200IMG_NO_SWEEP_SOBEL", 0) ||
+      (L.flags & B2I_LAUNCH_NO_TMA) || B2I_ENV("B200IMG_NO_TMA", 0))
     return 0;
   const PhaseDesc& ph = seg.phases[0];
   if (ph.type != PH_SOBEL || seg.cin != 3 || seg.cout != 3 || ph.expand || ph.border == B2I_BORDER_REF) return 0;
@@ -381,7 +381,7 @@ extern "C" int b2i_cuda_run_resident_fused(b2i_plan_t* plan, const b2i_launch_t*
   // the wait for the neighbour's rows of the pass before is over before it could hold anything up.
   P.strip_flags = (L.flags & B2I_LAUNCH_STRIP_FLAGS) ? 1 : 0;
   if (P.strip_flags && P.n_strips > B2I_MAX_STRIPS) B2I_FAIL(B2I_ERR_UNSUPPORTED, "image wider than the strip flags");
-  if (pushes && passes > 1 && y1 - y0 >= 4 * kS5Chunk && !env_int("B200IMG_NO_BSEG", 0)) {
+  if (pushes && passes > 1 && y1 - y0 >= 4 * kS5Chunk && !B2I_ENV("B200IMG_NO_BSEG", 0)) {
     P.bseg = kS5Chunk;
     const int mid = y1 - y0 - 2 * P.bseg;
     P.seg_rows = sweep_seg_rows(P.n_strips, mid, std::max(kS5Warps, resident - 2 * P.n_strips), kS5Chunk, 5, 120, 4);

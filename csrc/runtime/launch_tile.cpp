@@ -1,5 +1,6 @@
 // Tile-chain and pointwise launchers: tensor maps, shared-memory layout, tile height, grid.
 #include <algorithm>
+#include <atomic>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -83,13 +84,16 @@ void layout(const Segment& seg, int th, TileParams& P, int raw_stages) {
 }
 
 int device_sms(int dev, int* sms) {
-  static int cache[64] = {0};
-  if (dev >= 0 && dev < 64 && cache[dev]) {
-    *sms = cache[dev];
-    return B2I_OK;
+  static std::atomic<int> cache[64];   // zero-initialised; launches may come from several host threads
+  if (dev >= 0 && dev < 64) {
+    const int v = cache[dev].load(std::memory_order_relaxed);
+    if (v) {
+      *sms = v;
+      return B2I_OK;
+    }
   }
   B2I_CUDA(cudaDeviceGetAttribute(sms, cudaDevAttrMultiProcessorCount, dev));
-  if (dev >= 0 && dev < 64) cache[dev] = *sms;
+  if (dev >= 0 && dev < 64) cache[dev].store(*sms, std::memory_order_relaxed);
   return B2I_OK;
 }
 
@@ -114,7 +118,7 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
     // to the sweeps, and the tensor-core kernel takes what they cannot: one-channel planes, widths
     // that are not multiples of 8 pixels, and every stencil that is not separable (the tile kernel
     // needs 130 us and more for those). B200IMG_PREFER_MMA=1 turns the order around.
-    static const int prefer_mma = env_int("B200IMG_PREFER_MMA", 0);
+    static const int prefer_mma = B2I_ENV("B200IMG_PREFER_MMA", 0);
     int sw = try_sweep(plan, seg, L, y0, y1, src, dst, sms, last);
     if (sw == 0 && prefer_mma) sw = try_stencil_mma(plan, seg, L, y0, y1, src, dst, sms, first, last);
     if (sw == 0) sw = try_sweep5(plan, seg, L, y0, y1, src, dst, sms, first, last);
@@ -127,8 +131,8 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
   memset(&P, 0, sizeof P);
   // tile height: tallest that still lets two CTAs share an SM; smaller for small images so that
   // every SM gets tiles
-  int th = L.tile_h > 0 ? L.tile_h : env_int("B200IMG_TILE_H", 0);
-  int raw_stages = env_int("B200IMG_RAW_STAGES", 2);
+  int th = L.tile_h > 0 ? L.tile_h : B2I_ENV("B200IMG_TILE_H", 0);
+  int raw_stages = B2I_ENV("B200IMG_RAW_STAGES", 2);
   const int tiles_x = (L.W + kTileW - 1) / kTileW;
   if (th <= 0) {
     // Measured on 8K images (scripts/tile_h_sweep.py): the per-tile cost (barriers between
@@ -174,7 +178,7 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
   P.n_phases = (int)seg.phases.size();
   P.rgb_order = plan->chain.order == B2I_ORDER_RGB;
   P.raw_fix_border = seg.raw_fix_border;
-  P.debug = env_int("B200IMG_DEBUG", 0);
+  P.debug = B2I_ENV("B200IMG_DEBUG", 0);
   for (int k = 0; k < P.n_phases; ++k) {
     PhaseDesc& ph = P.ph[k];
     ph = seg.phases[k];
@@ -228,14 +232,14 @@ int launch_tile_segment(b2i_plan* plan, const Segment& seg, const b2i_launch_t& 
   P.dst_pitch = dst.pitch;
   P.dst_y_begin = y0;
   P.dst_y_end = y1;
-  const bool no_tma = (L.flags & B2I_LAUNCH_NO_TMA) || env_int("B200IMG_NO_TMA", 0);
+  const bool no_tma = (L.flags & B2I_LAUNCH_NO_TMA) || B2I_ENV("B200IMG_NO_TMA", 0);
   CUtensorMap src_map, dst_map, up_map, dn_map;
   memset(&src_map, 0, sizeof src_map);
   memset(&dst_map, 0, sizeof dst_map);
   memset(&up_map, 0, sizeof up_map);
   memset(&dn_map, 0, sizeof dn_map);
-  const bool no_tma_load = no_tma || env_int("B200IMG_NO_TMA_LOAD", 0);
-  const bool no_tma_store = no_tma || env_int("B200IMG_NO_TMA_STORE", 0) || (last && (L.flags & B2I_LAUNCH_DST_MCAST));
+  const bool no_tma_load = no_tma || B2I_ENV("B200IMG_NO_TMA_LOAD", 0);
+  const bool no_tma_store = no_tma || B2I_ENV("B200IMG_NO_TMA_STORE", 0) || (last && (L.flags & B2I_LAUNCH_DST_MCAST));
   P.use_tma_load = !no_tma_load && encode_map(&src_map, P.src_ptr, P.src_pitch, (int64_t)L.W * seg.cin,
                                          P.src_y_end - P.src_y_begin, kPlaneW * seg.cin, P.raw_rows);
   P.use_tma_store = !no_tma_store && encode_map(&dst_map, P.dst_ptr, P.dst_pitch, (int64_t)L.W * seg.cout,
@@ -356,7 +360,7 @@ int launch_pointwise_segment(b2i_plan* plan, const Segment& seg, const b2i_launc
   P.src_ptr = src.ptr + (uint64_t)((int64_t)(y0 - src.y_begin) * src.pitch);
   P.dst_ptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
   P.vec_ok = !((P.src_ptr | P.dst_ptr | (uint64_t)P.src_pitch | (uint64_t)P.dst_pitch) & 15) &&
-             !env_int("B200IMG_NO_VEC", 0);
+             !B2I_ENV("B200IMG_NO_VEC", 0);
   const long long units = (long long)((L.W + 511) / 512) * P.rows;  // one warp per 512-pixel run
   const long long want = (units + 7) / 8;
   const int grid = (int)std::max(1LL, std::min(want, (long long)sms * 8));

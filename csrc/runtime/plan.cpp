@@ -158,7 +158,7 @@ int build_tile_segment(const std::vector<Elem>& el, int cin, Segment& seg) {
       default: {  // stencil / sobel
         const b2i_op_t& op = *e.op;
         int wv[5] = {0, 0, 0, 0, 0}, wh[5] = {0, 0, 0, 0, 0};
-        if (!env_int("B200IMG_NO_SEP", 0) && separable(op, wv, wh)) {
+        if (!B2I_ENV("B200IMG_NO_SEP", 0) && separable(op, wv, wh)) {
           ph.type = PH_SEPH;  // horizontal pass: bytes -> 16-bit lanes
           ph.cout = c;
           ph.border = op.border;
@@ -412,7 +412,7 @@ int segment_chain(const std::vector<Elem>& el, int in_channels, bool split, std:
     if (!best.pointwise && !best.phases.empty() && best.phases[0].lut >= 0)
     {
       best.lut0_affine = affine_lut(best.luts[best.phases[0].lut], &best.aff_a, &best.aff_b, &best.aff_s);
-      if (env_int("B200IMG_DEBUG", 0) & 2)
+      if (B2I_ENV("B200IMG_DEBUG", 0) & 2)
         fprintf(stderr, "b200img: first LUT of segment %zu %s clamp((%d v + %d) >> %d)\n", out.size(),
                 best.lut0_affine ? "is" : "is not", best.aff_a, best.aff_b, best.aff_s);
     }
@@ -472,6 +472,13 @@ extern "C" int b2i_plan_create(const b2i_chain_t* chain, int in_channels, b2i_pl
 }
 
 extern "C" void b2i_plan_destroy(b2i_plan_t* plan) { delete plan; }
+// A plan keeps the figures of its last launch (b2i_plan_info: last_*), so one plan must not be
+// launched from two host threads at once; a thread that needs to gets its own copy.
+extern "C" int b2i_plan_clone(const b2i_plan_t* plan, b2i_plan_t** out) {
+  B2I_CHECK_ARG(plan && out, "null argument");
+  *out = new b2i_plan(*plan);
+  return B2I_OK;
+}
 extern "C" int b2i_plan_halo(const b2i_plan_t* plan) { return plan ? plan->halo : 0; }
 extern "C" int b2i_plan_info(const b2i_plan_t* plan, b2i_plan_info_t* info) {
   B2I_CHECK_ARG(plan && info, "null argument");
@@ -503,8 +510,8 @@ extern "C" int b2i_cuda_run(b2i_plan_t* plan, const b2i_launch_t* Lp) {
                          !(L.W & 7) && L.W >= 16 && L.H >= 8 && tma_ok(L.src) && tma_ok(L.dst) &&
                          tma_ok(L.tmp[0]) && (plan->segs_split.size() < 3 || tma_ok(L.tmp[1])) &&
                          L.tmp[0].pitch >= (int64_t)L.W * 3 && tensor_map_encoder() &&
-                         !env_int("B200IMG_NO_SWEEP", 0) && !env_int("B200IMG_NO_TMA", 0) &&
-                         !env_int("B200IMG_NO_SPLIT", 0);
+                         !B2I_ENV("B200IMG_NO_SWEEP", 0) && !B2I_ENV("B200IMG_NO_TMA", 0) &&
+                         !B2I_ENV("B200IMG_NO_SPLIT", 0);
   const std::vector<Segment>& segs = use_split ? plan->segs_split : plan->segs;
   const int n = (int)segs.size();
   // Degenerate images (narrower or shorter than a border fold can reach) and explicit requests
@@ -516,7 +523,7 @@ extern "C" int b2i_cuda_run(b2i_plan_t* plan, const b2i_launch_t* Lp) {
     B2I_CHECK_ARG(L.src.y_begin == 0 && L.dst.y_begin == 0 && L.src.y_end >= L.H && L.dst.y_end >= L.H,
                   "the reference-style path needs whole-image views");
     // LUT scratch: the tail of tmp[1] beyond its W*H*3 image bytes is not guaranteed, so LUTs
-    // live in the first tmp row of a third region the caller passes through `status`
+    // live in a third region that the caller passes through `counters`
     B2I_CHECK_ARG(L.counters, "the reference-style path needs 256*B2I_MAX_OPS bytes at `counters`");
     return run_naive(&plan->chain, reinterpret_cast<const uint8_t*>(L.src.ptr), L.W, L.H, plan->cin,
                      (size_t)L.src.pitch, reinterpret_cast<uint8_t*>(L.dst.ptr), (size_t)L.dst.pitch,

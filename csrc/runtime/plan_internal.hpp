@@ -58,6 +58,9 @@ struct Segment {
 
 // launch_tile.cpp
 int env_int(const char* name, int dflt);
+// The B200IMG_* switches are read once per process, at the first use of each call site: launches
+// do not walk the environment (they are debugging / A-B switches, set before the process starts).
+#define B2I_ENV(name, dflt) ([]() -> int { static const int v_ = ::b2i::env_int(name, dflt); return v_; }())
 int align_up(int v, int a);
 int device_sms(int dev, int* sms);
 PFN_cuTensorMapEncodeTiled_v12000 tensor_map_encoder();

@@ -52,6 +52,9 @@ typedef enum b2i_opkind {
 /* Border rule of a stencil.
  * REF: the defined subset of the reference's embossKernel guard (kernel.cu:83): pixels with
  *      x in [r+1, W-r-1] and y in [r+1, H-r-1] are filtered, every other pixel passes through.
+ *      That includes column W-r and row H-r, which the reference does filter, but from memory that
+ *      wraps into the next row or lies past the end of the band (kernel.cu:83): undefined there, so
+ *      passed through here.
  * REFLECT101: cv::filter2D default (kern.cpp:75). REPLICATE / ZERO: the usual meanings. */
 typedef enum b2i_border {
   B2I_BORDER_REF = 0,
@@ -106,7 +109,7 @@ int b2i_chain_describe(const b2i_chain_t* chain, char* buf, size_t buflen);
 void b2i_lut_contrast_ref(float factor, uint8_t* lut256); /* kernel.cu:56, fp32 + truncation */
 void b2i_lut_contrast_cv(double factor, uint8_t* lut256); /* kern.cpp:74, saturate_cast */
 
-/* ---- band planner (csrc/runtime/band_plan.cpp) ------------------------------------------ */
+/* ---- band planner (b2i_band_rows in csrc/host_ref/cpu_filters.cpp) ------------------------ */
 
 /* Rows [y0, y1) of band i of n over H rows: y0 = floor(i*H/n). Unlike kernel.cu:117 the
  * remainder rows are distributed, never dropped. */
@@ -231,6 +234,9 @@ typedef struct b2i_plan_info {
 
 int b2i_plan_create(const b2i_chain_t* chain, int in_channels, b2i_plan_t** out);
 void b2i_plan_destroy(b2i_plan_t* plan);
+/* A copy for another host thread: b2i_cuda_run records the figures of its last launch in the plan
+ * (b2i_plan_info last_*), so one plan is launched from one thread at a time. */
+int b2i_plan_clone(const b2i_plan_t* plan, b2i_plan_t** out);
 int b2i_plan_halo(const b2i_plan_t* plan);
 int b2i_plan_info(const b2i_plan_t* plan, b2i_plan_info_t* info);
 int b2i_cuda_run(b2i_plan_t* plan, const b2i_launch_t* launch);
