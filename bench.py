@@ -158,6 +158,10 @@ def main():
     ap.add_argument("--height", type=int, default=H8K)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
+    # stdout carries exactly one JSON line: whatever native libraries print there while the bench runs
+    # (NCCL's version banner, for one) goes to stderr instead
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         try:
             res = run_reference(args)
@@ -166,7 +170,8 @@ def main():
     else:
         res = run_ours(args)
     if rank == 0 and res is not None:
-        print(json.dumps(res), flush=True)
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(res) + "\n").encode())
 
 
 if __name__ == "__main__":
