@@ -10,11 +10,11 @@ import subprocess
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "mpi_cuda_imagemanipulation_b200", "lib", "libb200img.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
-EVID = ["UTMALDG.2D", "UTMASTG.2D", "UTMACCTL.PF", "UTMACMDFLUSH", "SYNCS.ARRIVE.TRANS64", "SYNCS.PHASECHK.TRANS64.TRYWAIT",
+EVID = ["UTCIMMA", "LDTM.x32", "STTM.x8", "UTCBAR", "UTCATOMSWS.FIND", "UTMALDG.2D", "UTMASTG.2D", "UTMACCTL.PF", "UTMACMDFLUSH", "SYNCS.ARRIVE.TRANS64", "SYNCS.PHASECHK.TRANS64.TRYWAIT",
         "SYNCS.EXCH.64", "IDP.4A.U8.S8", "FFMA.RM", "VIMNMX.U16x2", "FENCE.VIEW.ASYNC.S", "STG.E.STRONG.SYS", "LDG.E.STRONG.SYS",
         "ST.E.STRONG.SYS", "LD.E.STRONG.SYS", "LDG.E.NA.128.CONSTANT", "STG.E.NA.128", "STG.E.64", "ST.E.64", "SHFL.UP", "SHFL.DOWN",
         "I2IP", "PRMT", "IMAD", "LDS.64", "LDS.128", "STS.64", "STS.128", "LDS.U8"]
-HOT = ("sweep3_kernel<1, 2, false, 1>", "sweep5_kernel<false, true, true>", "sweep5_kernel<true, true, true>",
+HOT = ("stencil_mma_kernel<5, 1>", "stencil_mma_kernel<3, 2>", "sweep3_kernel<1, 2, false, 1>", "sweep5_kernel<false, true, true>", "sweep5_kernel<true, true, true>",
        "sweep_sobel_kernel<false>",
        "tile_chain_kernel", "pointwise_kernel<3, 1, false>", "pointwise_kernel<3, 0, false>")
 
