@@ -110,9 +110,12 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
     for (int i = 0; i < 12; ++i) PA[i] = DP[i] = SA[i] = SB[i] = 0;
 
     // one input row y; emits output row y-1. S1 holds S(y-1), S2 holds S(y-2) and takes S(y).
-    auto step = [&](auto qc, int c, const uint8_t* stage_base, uint32_t ob_prev, uint32_t ob_cur,
+    // SLOW (compile-time): the task also pushes halo rows or stores to a multicast image; every
+    // other task of a multi-GPU launch runs the single-GPU row loop (as in sweep5.cu).
+    auto step = [&](auto qc, auto slowc, int c, const uint8_t* stage_base, uint32_t ob_prev, uint32_t ob_cur,
                     uint32_t (&S1)[12], uint32_t (&S2)[12]) {
       constexpr int q = decltype(qc)::value;
+      constexpr bool SLOW = MG && decltype(slowc)::value;
       const int u = c * CH + q;
       const int y = ya - 1 + u;
       uint32_t a[8];
@@ -199,9 +202,9 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
           d[1] = make_uint2(r[2], r[3]);
           d[2] = make_uint2(r[4], r[5]);
         }
-        if (MG && P.push_rows && !halo_lane && !beyond)  // halo rows also go into the neighbours' ghost rows
+        if (SLOW && P.push_rows && !halo_lane && !beyond)  // halo rows also go into the neighbours' ghost rows
           sweep_push_row(P, y - 1, (int64_t)xs * 3 + (lane - 1) * 24, r);
-        if (MG && P.plain_dst_ptr && (er == CH - 1 || u == steps - 1)) {
+        if (SLOW && P.plain_dst_ptr && (er == CH - 1 || u == steps - 1)) {
           // NVLS: the box leaves in coalesced 16-byte stores to the multicast image, one store per
           // byte, and the switch writes every GPU's copy
           const int ec = (u - 2) / CH;
@@ -209,7 +212,7 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
                        P.plain_dst_ptr + (int64_t)(ya + ec * CH - P.y0) * P.plain_dst_pitch + (int64_t)xs * 3,
                        P.plain_dst_pitch, lane);
         }
-        if (!(MG && P.plain_dst_ptr) && (er == CH - 1 || u == steps - 1)) {  // a box of finished rows leaves by TMA
+        if (!(SLOW && P.plain_dst_ptr) && (er == CH - 1 || u == steps - 1)) {  // a box of finished rows leaves by TMA
           const int ec = (u - 2) / CH;
           fence_proxy_async_smem();
           __syncwarp();
@@ -221,6 +224,7 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
       }
     };
 
+    auto run_chunks = [&](auto slowc) {
     for (int c = 0; c < n_chunks; ++c) {
       const uint32_t st = (n_in + c) % NST;
       const uint8_t* stage_base = in_ring + st * P.in_stage_bytes;
@@ -231,10 +235,10 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
       // computed from whatever the box holds and never emitted. Skipping them costs a shuffle of
       // the 36 state registers at every join (measured here: 68.5 -> 65.4 us; the same change made
       // sweep3.cu and sweep5.cu slower, so those keep their conditional rows).
-      step(std::integral_constant<int, 0>{}, c, stage_base, ob_prev, ob_cur, SA, SB);
-      step(std::integral_constant<int, 1>{}, c, stage_base, ob_prev, ob_cur, SB, SA);
-      step(std::integral_constant<int, 2>{}, c, stage_base, ob_prev, ob_cur, SA, SB);
-      step(std::integral_constant<int, 3>{}, c, stage_base, ob_prev, ob_cur, SB, SA);
+      step(std::integral_constant<int, 0>{}, slowc, c, stage_base, ob_prev, ob_cur, SA, SB);
+      step(std::integral_constant<int, 1>{}, slowc, c, stage_base, ob_prev, ob_cur, SB, SA);
+      step(std::integral_constant<int, 2>{}, slowc, c, stage_base, ob_prev, ob_cur, SA, SB);
+      step(std::integral_constant<int, 3>{}, slowc, c, stage_base, ob_prev, ob_cur, SB, SA);
       __syncwarp();  // every lane has read the box: the stage can take box c + NST
       if (lane == 0 && c + NST < n_chunks) {
         mbar_arrive_expect_tx(&bar[st], CH * kSSInBytes);
@@ -242,6 +246,11 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
                     &bar[st]);
       }
     }
+    };
+    if (MG && ((P.push_rows && (ya < P.y0 + P.push_rows || yb > P.y1 - P.push_rows)) || P.plain_dst_ptr))
+      run_chunks(std::true_type{});
+    else
+      run_chunks(std::false_type{});
     n_in += n_chunks;
     n_out += (yb - ya + CH - 1) / CH;
     if (sig_up || sig_dn) sweep_signal_neighbours(P, sig_up, sig_dn, lane);
