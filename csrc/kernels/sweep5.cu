@@ -139,8 +139,8 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
     const int seg = so == 0 ? 0 : so == 1 ? P.n_segs - 1 : so - 1;
     int ya, yb;                                       // output rows [ya, yb)
     if (MG && P.bseg > 0) {   // short first / last segments: their halo rows are on the way early in the pass
-      ya = seg == 0 ? P.y0 : seg == P.n_segs - 1 ? P.y1 - P.bseg : P.y0 + P.bseg + (seg - 1) * P.seg_rows;
-      yb = seg == 0 ? P.y0 + P.bseg : seg == P.n_segs - 1 ? P.y1 : min(P.y1 - P.bseg, ya + P.seg_rows);
+      ya = seg == 0 ? P.y0 : seg == P.n_segs - 1 ? P.y1 - P.bseg_last : P.y0 + P.bseg + (seg - 1) * P.seg_rows;
+      yb = seg == 0 ? P.y0 + P.bseg : seg == P.n_segs - 1 ? P.y1 : min(P.y1 - P.bseg_last, ya + P.seg_rows);
     } else {
       ya = P.y0 + seg * P.seg_rows;
       yb = min(P.y1, ya + P.seg_rows);

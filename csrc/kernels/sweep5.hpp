@@ -45,7 +45,8 @@ struct Sweep5Params {
   // (wait_epoch + p) and signalled after every pass but the last (signal_epoch + p).
   int32_t n_passes;
   int32_t strip_flags;       // the neighbour flags are per-strip arrays (B2I_LAUNCH_STRIP_FLAGS)
-  int32_t bseg, reserved1;   // > 0: the first and the last segment are bseg rows (short, so that halos leave early)
+  int32_t bseg, bseg_last;   // > 0: the first segment is bseg rows and the last bseg_last (short, so that halos leave
+                             // early); the segments between are whole TMA boxes, the last one takes the remainder
   uint64_t task_done;                      // u32 per task in local memory, only ever growing
   uint64_t push_up_ptr_odd, push_dn_ptr_odd;  // the push targets of odd passes (the other buffer)
   uint8_t lut1[256];

@@ -229,10 +229,22 @@ int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0
   }
   P.n_strips = (L.W + kS5Strip - 1) / kS5Strip;
   const int resident = sms * kS5CtasPerSm * kS5Warps;
-  P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kS5Chunk, 5, 120, 4);
-  P.n_segs = (y1 - y0 + P.seg_rows - 1) / P.seg_rows;
+  if (pushes && y1 - y0 >= 4 * kS5Chunk && L.push_rows <= kS5Chunk && !B2I_ENV("B200IMG_NO_BSEG", 0)) {
+    // a launch that pushes halo rows: one-box first and last segments, which run first and are short,
+    // so the rows and the flag are with the neighbour while the other tasks still work
+    // (every segment but the last is whole boxes: a ragged box would spill into the rows below it)
+    P.bseg = kS5Chunk;
+    const int mid = (y1 - y0 - 2 * kS5Chunk) / kS5Chunk * kS5Chunk;
+    P.bseg_last = y1 - y0 - P.bseg - mid;
+    P.seg_rows = sweep_seg_rows(P.n_strips, mid, std::max(kS5Warps, resident - 2 * P.n_strips), kS5Chunk, 5, 120, 4);
+    P.n_segs = 2 + (mid + P.seg_rows - 1) / P.seg_rows;
+  } else {
+    P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kS5Chunk, 5, 120, 4);
+    P.n_segs = (y1 - y0 + P.seg_rows - 1) / P.seg_rows;
+  }
   P.n_tasks = P.n_strips * P.n_segs;
   if (pushes || flags) sweep_hooks_fill(P, L, y0, y1, first, last, pushes);
+  if (P.bseg) P.n_up_tasks = P.n_dn_tasks = P.n_strips;   // the short segments hold all the pushed rows
   const int grid = std::max(1, std::min((P.n_tasks + kS5Warps - 1) / kS5Warps, sms * kS5CtasPerSm));
   plan->info.last_tile_h = -P.seg_rows;
   plan->info.last_smem_bytes = P.warp_smem * kS5Warps;
@@ -382,8 +394,10 @@ extern "C" int b2i_cuda_run_resident_fused(b2i_plan_t* plan, const b2i_launch_t*
   P.strip_flags = (L.flags & B2I_LAUNCH_STRIP_FLAGS) ? 1 : 0;
   if (P.strip_flags && P.n_strips > B2I_MAX_STRIPS) B2I_FAIL(B2I_ERR_UNSUPPORTED, "image wider than the strip flags");
   if (pushes && passes > 1 && y1 - y0 >= 4 * kS5Chunk && !B2I_ENV("B200IMG_NO_BSEG", 0)) {
+    // (every segment but the last is whole boxes: a ragged box would spill into the rows below it)
     P.bseg = kS5Chunk;
-    const int mid = y1 - y0 - 2 * P.bseg;
+    const int mid = (y1 - y0 - 2 * kS5Chunk) / kS5Chunk * kS5Chunk;
+    P.bseg_last = y1 - y0 - P.bseg - mid;
     P.seg_rows = sweep_seg_rows(P.n_strips, mid, std::max(kS5Warps, resident - 2 * P.n_strips), kS5Chunk, 5, 120, 4);
     P.n_segs = 2 + (mid + P.seg_rows - 1) / P.seg_rows;
   } else {
