@@ -42,7 +42,15 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
     return 0;
   const bool finish = last && (L.done_flag || L.wait_done_mask);
   if (finish && !(L.counters && L.status)) return 0;
-  if ((L.W & 7) || L.W < 16 || y1 - y0 < 1) return 0;
+  // Widths that are not a multiple of 8 pixels: fine under the reference's border rule (kernel.cu:83:
+  // the last columns pass through, nothing is mirrored at a lane boundary) when the rows have room for
+  // the tensor maps' 4-byte granularity, i.e. in pitched buffers. Mirrored / replicated borders fold
+  // at lane boundaries and keep the multiple-of-8 rule (the tensor-core kernel takes those).
+  const int64_t in_row = ((int64_t)L.W * 3 + 3) & ~3LL, out_row_b = ((int64_t)L.W * seg.cout + 3) & ~3LL;
+  if (L.W & 7) {
+    if (st.border != B2I_BORDER_REF || src.pitch < in_row || dst.pitch < out_row_b) return 0;
+  }
+  if (L.W < 16 || y1 - y0 < 1) return 0;
   SweepParams P;
   memset(&P, 0, sizeof P);
   P.W = L.W;
@@ -73,7 +81,7 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
   P.warp_smem = kSweepStages * P.in_stage_bytes + 2 * P.out_buf_bytes + 128;  // + dummy slot for the halo lanes
   CUtensorMap src_map, dst_map;
   const int src_rows = std::min(src.y_end, L.H) - src.y_begin;
-  if (!encode_map(&src_map, src.ptr, src.pitch, (int64_t)L.W * 3, src_rows, kSweepInBytes, kSweepChunk)) return 0;
+  if (!encode_map(&src_map, src.ptr, src.pitch, in_row, src_rows, kSweepInBytes, kSweepChunk)) return 0;
   const uint64_t dptr = dst.ptr + (uint64_t)((int64_t)(y0 - dst.y_begin) * dst.pitch);
   const bool plain = last && (L.flags & B2I_LAUNCH_DST_MCAST);
   if (plain) {  // NVLS multicast image: 16-byte stores from the staging buffer, no tensor map on that address
@@ -81,7 +89,7 @@ int try_sweep(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0,
     memset(&dst_map, 0, sizeof dst_map);
     P.plain_dst_ptr = dptr;
     P.plain_dst_pitch = dst.pitch;
-  } else if (!encode_map(&dst_map, dptr, dst.pitch, (int64_t)L.W * seg.cout, y1 - y0, out_row, kSweepChunk)) {
+  } else if (!encode_map(&dst_map, dptr, dst.pitch, out_row_b, y1 - y0, out_row, kSweepChunk)) {
     return 0;
   }
   // segment height: a multiple of the box height, chosen so that the tasks fill the resident

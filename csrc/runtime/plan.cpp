@@ -503,11 +503,12 @@ extern "C" int b2i_cuda_run(b2i_plan_t* plan, const b2i_launch_t* Lp) {
   if (L.y0 == L.y1) return B2I_OK;
   NvtxRange range("b2i_cuda_run");
   plan->info.last_launches = 0;
-  // the split cut only where the sweep kernels can take it: 8-pixel widths, TMA-encodable views
+  // the split cut only where the sweep / tensor-core kernels can take it: TMA-encodable views (16-byte
+  // pitches; the kernels check the widths they need themselves)
   // and tmp images; anything else runs the fused cut on the tile kernel
   auto tma_ok = [](const b2i_view_t& v) { return v.ptr && !(v.ptr & 15) && !(v.pitch & 15); };
   const bool use_split = !plan->segs_split.empty() && !(L.flags & (B2I_LAUNCH_NO_TMA | B2I_LAUNCH_NAIVE)) &&
-                         !(L.W & 7) && L.W >= 16 && L.H >= 8 && tma_ok(L.src) && tma_ok(L.dst) &&
+                         L.W >= 16 && L.H >= 8 && tma_ok(L.src) && tma_ok(L.dst) &&
                          tma_ok(L.tmp[0]) && (plan->segs_split.size() < 3 || tma_ok(L.tmp[1])) &&
                          L.tmp[0].pitch >= (int64_t)L.W * 3 && tensor_map_encoder() &&
                          !B2I_ENV("B200IMG_NO_SWEEP", 0) && !B2I_ENV("B200IMG_NO_TMA", 0) &&

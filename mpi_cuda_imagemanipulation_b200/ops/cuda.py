@@ -62,14 +62,21 @@ class Plan:
     def scratch(self, device, W: int, H: int):
         key = (str(device), W, H)
         if key not in self._tmp:
-            self._tmp[key] = (torch.empty(H * W * 3, dtype=torch.uint8, device=device),
-                              torch.empty(H * W * 3, dtype=torch.uint8, device=device),
+            pitch = (W * 3 + 127) // 128 * 128     # pitched: TMA needs a 16-byte row pitch at any width
+            self._tmp[key] = (torch.empty(H * pitch, dtype=torch.uint8, device=device),
+                              torch.empty(H * pitch, dtype=torch.uint8, device=device),
                               torch.zeros(256 * _lib.B2I_MAX_OPS, dtype=torch.uint8, device=device))
         return self._tmp[key]
 
     def run(self, src: torch.Tensor, out: Optional[torch.Tensor] = None, *, naive: bool = False,
-            no_tma: bool = False, tile_h: int = 0) -> torch.Tensor:
-        """dst = chain(src) for a whole HxWxC uint8 CUDA tensor on the current stream."""
+            no_tma: bool = False, tile_h: int = 0, stage: Optional[bool] = None) -> torch.Tensor:
+        """dst = chain(src) for a whole HxWxC uint8 CUDA tensor on the current stream.
+
+        ``stage``: tightly packed images whose row length is not a multiple of 16 bytes cannot be
+        addressed by TMA. By default (None) such an image of 64 Ki pixels or more is copied into a
+        pitched buffer of this plan, filtered there by the fast kernels and copied back (two extra
+        passes over memory, still well ahead of the plain-loader kernel); False keeps it where it is.
+        Images that already live in pitched buffers (``pitched_empty``) need neither."""
         if not src.is_cuda or src.dtype != torch.uint8:
             raise TypeError("expected a uint8 CUDA tensor")
         H, W, Cn = image_geometry(src)
@@ -87,6 +94,20 @@ class Plan:
             raise ValueError("out must be contiguous, or rows of packed pixels at a row pitch (see pitched_empty)")
         dst_pitch = W * self.cout if out.is_contiguous() else out.stride(0)
         flags = (_lib.LAUNCH_NAIVE if naive else 0) | (_lib.LAUNCH_NO_TMA if no_tma else 0)
+        if stage is None:
+            stage = W * H >= 65536
+        if stage and not naive and not no_tma and ((src_pitch | dst_pitch) & 15 or (src.data_ptr() | out.data_ptr()) & 15):
+            key = ("stage", str(src.device), W, H)
+            if key not in self._tmp:
+                self._tmp[key] = (pitched_empty(H, W, Cn, src.device), pitched_empty(H, W, self.cout, src.device))
+            sp, dp = self._tmp[key]
+            stream = torch.cuda.current_stream().cuda_stream
+            with torch.cuda.device(src.device):   # 2-D device copies (cudaMemcpy2DAsync), rows of W*C bytes
+                check(lib.b2i_cuda_memcpy2d(sp.data_ptr(), sp.stride(0), src.data_ptr(), src_pitch, W * Cn, H, 2, stream))
+                self.run(sp, dp, tile_h=tile_h, stage=False)
+                check(lib.b2i_cuda_memcpy2d(out.data_ptr(), dst_pitch, dp.data_ptr(), dp.stride(0), W * self.cout, H, 2,
+                                            stream))
+            return out
         need_tmp = naive or self.n_segments > 1 or (self.halo > 0 and (W <= 16 or H <= 16))
         t0 = t1 = ls = None
         if need_tmp:
@@ -97,8 +118,9 @@ class Plan:
             L.src = View(src.data_ptr(), src_pitch, 0, H)
             L.dst = View(out.data_ptr(), dst_pitch, 0, H)
             if need_tmp:
-                L.tmp[0] = View(t0.data_ptr(), W * 3, 0, H)
-                L.tmp[1] = View(t1.data_ptr(), W * 3, 0, H)
+                tp = (W * 3 + 127) // 128 * 128
+                L.tmp[0] = View(t0.data_ptr(), tp, 0, H)
+                L.tmp[1] = View(t1.data_ptr(), tp, 0, H)
                 L.counters = ls.data_ptr()
             L.stream = torch.cuda.current_stream().cuda_stream
             L.tile_h = tile_h

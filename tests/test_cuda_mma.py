@@ -80,3 +80,19 @@ def test_gray_then_blur_is_two_launches():
     info = plan.info()
     assert info["launches"] == 2 and info["tile_h"] == 128, info
     assert np.array_equal(out.cpu().numpy().reshape(2160, 3840), b2.host_run("gray,gauss5", img).reshape(2160, 3840))
+
+
+@pytest.mark.parametrize("W,H", [(1001, 1001), (7681, 90), (1917, 300), (523, 64)])
+def test_reference_pipeline_on_odd_widths_in_pitched_buffers(W, H):
+    """kernel_cu (border = ref, kernel.cu:83) keeps the sweep kernel on any width when the rows are pitched:
+    `tile_h < 0` is the sweep kernels' signature (minus the rows per segment)."""
+    from mpi_cuda_imagemanipulation_b200.ops.cuda import Plan, pitched_empty
+    img = b2.synth_image(W, H, 3, seed=8)
+    plan = Plan("kernel_cu", 3)
+    src = pitched_empty(H, W, 3)
+    src.copy_(torch.from_numpy(img).cuda())
+    out = pitched_empty(H, W, 3)
+    plan.run(src, out)
+    torch.cuda.synchronize()
+    assert plan.info()["tile_h"] < 0, plan.info()
+    assert np.array_equal(out.cpu().numpy(), b2.host_run("kernel_cu", img))
