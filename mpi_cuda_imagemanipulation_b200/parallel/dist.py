@@ -591,6 +591,10 @@ def bench_distributed(args, rank: int, world: int, local: int) -> Optional[dict]
                                 f"the root's one NVLink port) and a few larger ones, timed as whole steps; 1.000 means the "
                                 f"link cannot pay for itself on this filter and the root keeps the image",
                        "equal_bands_ms_per_step": round(ms_equal, 6),
+                       "equal_bands_of_link_roofline": round((world - 1) / world * W * H * 3 / 770e9 * 1e3 / ms_equal, 3),
+                       "link_roofline": "(N-1)/N of the 99.5 MB image leaves GPU 0 and as much enters it, per direction at the "
+                                        "770 GB/s of a peer copy; the fused scatter / gather (TMA over NVLink) reaches the "
+                                        "fraction above, which is why the calibrated plan keeps the image on the root",
                        "l2": "input 99.5 MB + output 99.5 MB per step; remote ranks bypass the root's L2 for peer traffic",
                        "timed_as": f"{K} steps per replay from C, CUDA events per rank, max over ranks, median of {args.repeats}"},
             "clocks": clk.summary(),
