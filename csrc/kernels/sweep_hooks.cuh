@@ -5,6 +5,8 @@
 #include "device_utils.cuh"
 #include "sweep5.hpp"
 
+#include <type_traits>
+
 namespace b2i {
 namespace dev {
 
@@ -47,7 +49,7 @@ __device__ __forceinline__ void sweep_push_row(const Params& P, int oy, int64_t 
                                                bool odd = false) {
   // (resident multi-pass launches push into the other band buffer on odd passes: sweep5.hpp)
   uint64_t up = P.push_up_ptr, dn = P.push_dn_ptr;
-  if constexpr (sizeof(Params) == sizeof(Sweep5Params)) {
+  if constexpr (std::is_same<Params, Sweep5Params>::value) {
     if (odd) {
       up = reinterpret_cast<const Sweep5Params&>(P).push_up_ptr_odd;
       dn = reinterpret_cast<const Sweep5Params&>(P).push_dn_ptr_odd;

@@ -83,7 +83,14 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
     // boundary segments first: their rows feed the neighbours' next pass
     const int so = task / P.n_strips, strip = task - so * P.n_strips;
     const int seg = so == 0 ? 0 : so == 1 ? P.n_segs - 1 : so - 1;
-    const int ya = P.y0 + seg * P.seg_rows, yb = min(P.y1, ya + P.seg_rows);  // output rows [ya, yb)
+    int ya, yb;                                       // output rows [ya, yb)
+    if (MG && P.bseg > 0) {   // short first / last segments: their halo rows are on the way early in the pass
+      ya = seg == 0 ? P.y0 : seg == P.n_segs - 1 ? P.y1 - P.bseg_last : P.y0 + P.bseg + (seg - 1) * P.seg_rows;
+      yb = seg == 0 ? P.y0 + P.bseg : seg == P.n_segs - 1 ? P.y1 : min(P.y1 - P.bseg_last, ya + P.seg_rows);
+    } else {
+      ya = P.y0 + seg * P.seg_rows;
+      yb = min(P.y1, ya + P.seg_rows);
+    }
     const int steps = yb - ya + 2;                   // input rows ya-1 .. yb
     const int n_chunks = (steps + CH - 1) / CH;
     const int xs = strip * kSSStrip;

@@ -23,6 +23,7 @@ struct SweepSobelParams {
   // multi-GPU hooks, as in sweep5.hpp
   int32_t push_rows, push_pitch;
   int32_t n_up_tasks, n_dn_tasks;
+  int32_t bseg, bseg_last;   // > 0: short first / last segments (one TMA box; the last takes the remainder), as in sweep5.hpp
   uint32_t wait_epoch, signal_epoch;
   uint64_t push_up_ptr, push_dn_ptr;
   uint64_t wait_up_flag, wait_dn_flag, signal_up_flag, signal_dn_flag;

@@ -309,10 +309,20 @@ int try_sweep_sobel(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, i
   }
   P.n_strips = (L.W + kSSStrip - 1) / kSSStrip;
   const int resident = sms * kSSCtasPerSm * kSSWarps;
-  P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kSSChunk, 4, 120, 2);
-  P.n_segs = (y1 - y0 + P.seg_rows - 1) / P.seg_rows;
+  if (pushes && y1 - y0 >= 4 * kSSChunk && L.push_rows <= kSSChunk && !B2I_ENV("B200IMG_NO_BSEG", 0)) {
+    // one-box first and last segments when halo rows are pushed (see try_sweep5)
+    P.bseg = kSSChunk;
+    const int mid = (y1 - y0 - 2 * kSSChunk) / kSSChunk * kSSChunk;
+    P.bseg_last = y1 - y0 - P.bseg - mid;
+    P.seg_rows = sweep_seg_rows(P.n_strips, mid, std::max(kSSWarps, resident - 2 * P.n_strips), kSSChunk, 4, 120, 2);
+    P.n_segs = 2 + (mid + P.seg_rows - 1) / P.seg_rows;
+  } else {
+    P.seg_rows = sweep_seg_rows(P.n_strips, y1 - y0, resident, kSSChunk, 4, 120, 2);
+    P.n_segs = (y1 - y0 + P.seg_rows - 1) / P.seg_rows;
+  }
   P.n_tasks = P.n_strips * P.n_segs;
   if (pushes || flags) sweep_hooks_fill(P, L, y0, y1, first, last, pushes);
+  if (P.bseg) P.n_up_tasks = P.n_dn_tasks = P.n_strips;
   const int grid = std::max(1, std::min((P.n_tasks + kSSWarps - 1) / kSSWarps, sms * kSSCtasPerSm));
   plan->info.last_tile_h = -P.seg_rows;
   plan->info.last_smem_bytes = P.warp_smem * kSSWarps;
