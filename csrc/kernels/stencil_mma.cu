@@ -78,22 +78,11 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 // Shared-memory matrix descriptor (Blackwell format: version 1 in bits 46-47).
 //   layout 2 = 128-byte swizzle, K-major: rows 128 bytes apart, SBO between 8-row groups
 //   layout 0 = no swizzle, K-major: 8 x 16-byte core matrices, LBO between the two K halves, SBO between 8-row groups
-__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo, uint32_t base_off,
-                                              uint32_t layout) {
-  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) |
-         (1ull << 46) | ((uint64_t)(base_off & 7u) << 49) | ((uint64_t)layout << 61);
-}
+// (the 64-bit descriptor: start address >> 4 in bits 0-13, LBO >> 4 in bits 16-29, SBO >> 4 in bits 32-45,
+// version 1 in bits 46-47, base offset in bits 49-51 -- left 0, see the header comment -- layout in bits 61-63)
 
 // D[tmem] += A[smem] x B[smem], A unsigned bytes, B signed bytes, D s32, M = 128.
-__device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}"
-      ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(1u), "r"(0u), "r"(0u), "r"(0u), "r"(0u)
-      : "memory");
-}
-// The same with the descriptors as (lo, hi) words: the issuing thread only ever adds small
+// The descriptors travel as (lo, hi) words: the issuing thread only ever adds small
 // constants to the lo words (start address field), the hi words are compile-time constants.
 __device__ __forceinline__ void umma_i8_w(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
                                           uint32_t idesc) {

@@ -377,6 +377,12 @@ int b2i_cuda_run_resident_fused(b2i_plan_t* plan, const b2i_launch_t* even, cons
                                 uint32_t epoch_base, uint64_t task_flags, int n_task_flags);
 int b2i_cuda_memcpy2d(uint64_t dst, size_t dpitch, uint64_t src, size_t spitch, size_t width,
                       size_t height, int kind /*0 H2D, 1 D2H, 2 D2D*/, void* stream);
+/* Experiment (kernels/cluster_probe.cu): neighbouring stencil tiles of T rows load the 2R rows they
+ * share twice (one TMA box per CTA) or once (a two-CTA cluster, the shared rows by one multicast TMA load
+ * into both CTAs' shared memory). Runs both on a W3-byte x H-row image it allocates on the current GPU;
+ * time per launch of each and the number of wrong output bytes (0). */
+int b2i_cuda_cluster_probe(int W3, int H, int T, int R, int iters, float* us_plain, float* us_cluster,
+                           long long* mismatches);
 
 #ifdef __cplusplus
 }

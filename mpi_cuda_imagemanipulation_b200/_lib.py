@@ -190,6 +190,8 @@ _sig("b2i_cuda_run_host_image", C.c_int, _P(ChainStruct), u8p, C.c_int, C.c_int,
      C.c_size_t, u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, _P(C.c_double), _P(C.c_double))
 
 NOALLOC_MAX_PIXELS = 2 * 1024 * 1024
+_sig("b2i_cuda_cluster_probe", C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float),
+     C.POINTER(C.c_float), C.POINTER(C.c_longlong))
 _sig("b2i_cuda_run_image_noalloc", C.c_int, C.c_void_p, C.c_uint64, C.c_int64, C.c_uint64, C.c_int64,
      C.c_int, C.c_int, C.c_void_p, C.c_int)
 
