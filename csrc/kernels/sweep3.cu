@@ -128,7 +128,10 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
   uint32_t n_in = 0;   // input chunks consumed by this warp so far (stage = n_in % NST)
   uint32_t n_out = 0;  // output chunks stored so far (buffer = n_out & 1)
   const int total_warps = gridDim.x * kWarps;
-  for (int task = blockIdx.x * kWarps + warp; task < P.n_tasks; task += total_warps) {
+  // Fewer tasks than warps (small bands): warp w of CTA c is global warp w * gridDim.x + c, so every SM gets
+  // its share of the busy warps instead of some SMs a full CTA and others none. Otherwise CTA by CTA.
+  const int global_warp = P.n_tasks < total_warps ? warp * (int)gridDim.x + (int)blockIdx.x : (int)blockIdx.x * kWarps + warp;
+  for (int task = global_warp; task < P.n_tasks; task += total_warps) {
     const int seg = task / P.n_strips, strip = task - seg * P.n_strips;
     const int ya = P.y0 + seg * P.seg_rows, yb = min(P.y1, ya + P.seg_rows);  // output rows [ya, yb)
     const int steps = yb - ya + 2;                   // gray rows ya-1 .. yb
@@ -328,7 +331,7 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
     n_in += n_chunks;
     n_out += (yb - ya + CH - 1) / CH;
   }
-  sweep_kernel_end(P, blockIdx.x * kWarps + warp, total_warps, lane);
+  sweep_kernel_end(P, global_warp, total_warps, lane);
 }
 
 }  // namespace

@@ -124,6 +124,9 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
 
   uint32_t n_in = 0, n_out = 0;  // boxes consumed / stored by this warp so far
   const int total_warps = gridDim.x * kS5Warps;
+  // Fewer tasks than warps (small bands): warp w of CTA c is global warp w * gridDim.x + c, so every SM gets
+  // its share of the busy warps instead of some SMs a full CTA and others none. Otherwise CTA by CTA.
+  const int global_warp = P.n_tasks < total_warps ? warp * (int)gridDim.x + (int)blockIdx.x : (int)blockIdx.x * kS5Warps + warp;
   // Resident multi-pass launches walk the passes here; every other launch is one pass.
   const int n_passes = MG ? max(1, P.n_passes) : 1;
   for (int pass = 0; pass < n_passes; ++pass) {
@@ -133,7 +136,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
   const bool multi = MG && n_passes > 1;
   const bool wait_nb = MG && (!multi || pass > 0);             // ghost rows of pass 0 come from the scatter
   const bool push_nb = MG && (!multi || pass + 1 < n_passes);  // nobody reads the last pass's halo
-  for (int task = blockIdx.x * kS5Warps + warp; task < P.n_tasks; task += total_warps) {
+  for (int task = global_warp; task < P.n_tasks; task += total_warps) {
     // boundary segments first: their rows feed the neighbours' next pass
     const int so = task / P.n_strips, strip = task - so * P.n_strips;
     const int seg = so == 0 ? 0 : so == 1 ? P.n_segs - 1 : so - 1;
@@ -375,7 +378,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
     }
   }
   }
-  sweep_kernel_end(P, blockIdx.x * kS5Warps + warp, total_warps, lane);
+  sweep_kernel_end(P, global_warp, total_warps, lane);
 }
 
 }  // namespace
@@ -399,7 +402,7 @@ cudaError_t launch_sweep5(const Sweep5Params& P, const CUtensorMap& src_map, con
       sweep5_kernel<true, true, false>,   sweep5_kernel<true, true, true>};
   const Kern kern = table[variant];
   if (dev < 64 && !configured[dev][variant]) {
-    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P.warp_smem * kS5Warps);
     if (e != cudaSuccess) return e;
     configured[dev][variant] = true;
   }

@@ -4,8 +4,8 @@
 
 namespace b2i {
 
-constexpr int kS5Warps = 7;        // warps per CTA; 2 CTAs per SM = 14 warps (shared memory bound)
-constexpr int kS5CtasPerSm = 2;
+constexpr int kS5Warps = 14;       // warps per CTA; 1 CTA per SM (shared memory bound): 4 + 4 + 3 + 3 on the schedulers (two CTAs of 7 measured 3 % slower)
+constexpr int kS5CtasPerSm = 1;
 constexpr int kS5Strip = 240;      // output pixels per warp row: 30 lanes x 8 pixels (lanes 0, 31 are halo)
 constexpr int kS5InBytes = 800;    // TMA box width: 32 bytes left of the strip + 32 lanes x 24 bytes
 constexpr int kS5OutBytes = 720;   // 240 pixels x 3 channels

@@ -79,7 +79,10 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
 
   uint32_t n_in = 0, n_out = 0;  // boxes consumed / stored by this warp so far
   const int total_warps = gridDim.x * kSSWarps;
-  for (int task = blockIdx.x * kSSWarps + warp; task < P.n_tasks; task += total_warps) {
+  // Fewer tasks than warps (small bands): warp w of CTA c is global warp w * gridDim.x + c, so every SM gets
+  // its share of the busy warps instead of some SMs a full CTA and others none. Otherwise CTA by CTA.
+  const int global_warp = P.n_tasks < total_warps ? warp * (int)gridDim.x + (int)blockIdx.x : (int)blockIdx.x * kSSWarps + warp;
+  for (int task = global_warp; task < P.n_tasks; task += total_warps) {
     // boundary segments first: their rows feed the neighbours' next pass
     const int so = task / P.n_strips, strip = task - so * P.n_strips;
     const int seg = so == 0 ? 0 : so == 1 ? P.n_segs - 1 : so - 1;
@@ -262,7 +265,7 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
     n_out += (yb - ya + CH - 1) / CH;
     if (sig_up || sig_dn) sweep_signal_neighbours(P, sig_up, sig_dn, lane);
   }
-  sweep_kernel_end(P, blockIdx.x * kSSWarps + warp, total_warps, lane);
+  sweep_kernel_end(P, global_warp, total_warps, lane);
 }
 
 }  // namespace
