@@ -55,6 +55,16 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32
   }
 }
 
+// ---- programmatic dependent launch ---------------------------------------------------------------------
+// A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start while the kernel
+// before it in the stream is still running, once every CTA of that kernel has called
+// pdl_launch_dependents() (or exited). Everything before pdl_wait() must not touch memory the earlier
+// kernel writes: the sweeps run their prologue there (barrier init, table copy, descriptor prefetch).
+// pdl_wait() returns when the earlier kernel has completed and its writes are visible. Both are no-ops in
+// a launch without the attribute.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- TMA ------------------------------------------------------------------------------------
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");

@@ -8,6 +8,7 @@
 // the gather (kernel.cu:223).
 #include "b200img.h"
 #include "device_utils.cuh"
+#include "launch_pdl.hpp"
 #include "tile_plan.hpp"
 
 namespace b2i {
@@ -79,11 +80,13 @@ pointwise_kernel(const __grid_constant__ PointwiseParams P) {
   __shared__ __align__(16) uint8_t lut0[256];
   __shared__ __align__(16) uint8_t lut1[256];
   __shared__ __align__(16) uint8_t xpose[kPwThreads / 32][1536];
+  pdl_launch_dependents();   // the next launch in the stream may set itself up behind this one
   for (int i = threadIdx.x; i < 64; i += kPwThreads) {
     reinterpret_cast<uint32_t*>(lut0)[i] = reinterpret_cast<const uint32_t*>(P.lut0)[i];
     reinterpret_cast<uint32_t*>(lut1)[i] = reinterpret_cast<const uint32_t*>(P.lut1)[i];
   }
   __syncthreads();
+  pdl_wait();   // the launch before this one has completed: its output may be this one's input
   constexpr int COUT = GRAY ? (EXPAND ? 3 : 1) : (EXPAND ? 3 : CIN);
   constexpr int MID = GRAY ? 1 : CIN;          // channels between the two LUTs
   constexpr bool BYTEWISE = !GRAY && !EXPAND;  // C -> C per byte: no pixel structure needed
@@ -208,17 +211,18 @@ pointwise_kernel(const __grid_constant__ PointwiseParams P) {
 
 cudaError_t launch_pointwise(const PointwiseParams& P, int grid, cudaStream_t stream) {
   const int key = P.cin * 100 + P.gray * 10 + (P.expand ? 1 : 0);
+  cudaError_t e = cudaSuccess;
   switch (key) {
-    case 310: pointwise_kernel<3, 1, false><<<grid, kPwThreads, 0, stream>>>(P); break;
-    case 311: pointwise_kernel<3, 1, true><<<grid, kPwThreads, 0, stream>>>(P); break;
-    case 320: pointwise_kernel<3, 2, false><<<grid, kPwThreads, 0, stream>>>(P); break;
-    case 321: pointwise_kernel<3, 2, true><<<grid, kPwThreads, 0, stream>>>(P); break;
-    case 300: pointwise_kernel<3, 0, false><<<grid, kPwThreads, 0, stream>>>(P); break;
-    case 100: pointwise_kernel<1, 0, false><<<grid, kPwThreads, 0, stream>>>(P); break;
-    case 101: pointwise_kernel<1, 0, true><<<grid, kPwThreads, 0, stream>>>(P); break;
+    case 310: e = launch_pdl(pointwise_kernel<3, 1, false>, grid, kPwThreads, 0, stream, P); break;
+    case 311: e = launch_pdl(pointwise_kernel<3, 1, true>, grid, kPwThreads, 0, stream, P); break;
+    case 320: e = launch_pdl(pointwise_kernel<3, 2, false>, grid, kPwThreads, 0, stream, P); break;
+    case 321: e = launch_pdl(pointwise_kernel<3, 2, true>, grid, kPwThreads, 0, stream, P); break;
+    case 300: e = launch_pdl(pointwise_kernel<3, 0, false>, grid, kPwThreads, 0, stream, P); break;
+    case 100: e = launch_pdl(pointwise_kernel<1, 0, false>, grid, kPwThreads, 0, stream, P); break;
+    case 101: e = launch_pdl(pointwise_kernel<1, 0, true>, grid, kPwThreads, 0, stream, P); break;
     default: return cudaErrorInvalidValue;
   }
-  return cudaGetLastError();
+  return e;
 }
 
 }  // namespace b2i

@@ -40,6 +40,7 @@
 // one thread per pixel and seven byte loads per output; kern.cpp:75 is cv::filter2D.
 #include "b200img.h"
 #include "device_utils.cuh"
+#include "launch_pdl.hpp"
 #include "stencil_mma.hpp"
 
 namespace b2i {
@@ -182,6 +183,7 @@ stencil_mma_kernel(const __grid_constant__ StencilMmaParams P, const __grid_cons
   __shared__ __align__(16) int8_t wtab[2][kSmMaxDy][112];  // weight of input byte i for result byte o, at [d = i - o + 48]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_launch_dependents();   // the next launch in the stream may set itself up behind this one
   if (threadIdx.x == 0) stamp(P, 0);
   constexpr int ndy = NDY, nacc = NACC;      // NDY = 2R + 1; NACC = 2: Sobel's gx and gy
   constexpr int ring = kSmRing / nacc;      // columns per accumulator
@@ -228,6 +230,8 @@ stencil_mma_kernel(const __grid_constant__ StencilMmaParams P, const __grid_cons
   if (warp == 0) {
     // ===== TMA producer =====================================================================
     if (lane == 0) {
+      pdl_wait();   // the launch before this one has completed: its output may be this one's input. The
+                    // other warps build the band matrices meanwhile (3 us that hide behind that launch).
       uint32_t n = 0;
       int g = g_lo;
       Run r;
@@ -444,6 +448,7 @@ stencil_mma_kernel(const __grid_constant__ StencilMmaParams P, const __grid_cons
       tmem_st_wait();
       tc_fence_before();
       asm volatile("bar.sync 2, 160;" ::: "memory");
+      pdl_wait();   // (the results depend on the producer's loads anyway; this orders the stores explicitly)
       const bool fast8 = NACC == 1 && P.fast8;
       const bool leader = threadIdx.x == 64;
       uint32_t C = 0, n_store = 0;
@@ -558,8 +563,7 @@ cudaError_t launch_stencil_mma(const StencilMmaParams& P, const CUtensorMap& src
     if (e != cudaSuccess) return e;
     configured[dev][variant] = true;
   }
-  kern<<<grid, kSmThreads, smem, stream>>>(P, src_map, dst_map);
-  return cudaGetLastError();
+  return launch_pdl(kern, grid, kSmThreads, smem, stream, P, src_map, dst_map);
 }
 
 }  // namespace b2i

@@ -19,6 +19,7 @@
 // Source and destination may be peer memory (scatter / gather fused), exactly as in tile_chain.cu.
 #include "b200img.h"
 #include "device_utils.cuh"
+#include "launch_pdl.hpp"
 #include "sweep_hooks.cuh"
 #include "sweep3.hpp"
 
@@ -96,6 +97,7 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
   __shared__ __align__(256) uint8_t lut1[256];
   __shared__ __align__(8) uint64_t bars[kWarps * NST];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_launch_dependents();   // the next launch in the stream may set itself up behind this one
   for (int i = threadIdx.x; i < 64; i += kWarps * 32) {
     reinterpret_cast<uint32_t*>(lut0)[i] = reinterpret_cast<const uint32_t*>(P.lut0)[i];
     reinterpret_cast<uint32_t*>(lut1)[i] = reinterpret_cast<const uint32_t*>(P.lut1)[i];
@@ -107,6 +109,7 @@ sweep3_kernel(const __grid_constant__ SweepParams P, const __grid_constant__ CUt
     if (!PLAIN) tma_prefetch_desc(&dst_map);
   }
   __syncthreads();  // the only block-wide barrier of the kernel
+  pdl_wait();       // the launch before this one has completed: its output may be this one's input
 
   const bool expand = SPEC != 0 || P.expand;
   const int out_pitch = expand ? kSweepOutBytes : kSweepStrip;  // staged bytes per output row
@@ -359,8 +362,7 @@ cudaError_t launch_sweep3(const SweepParams& P, const CUtensorMap& src_map, cons
     if (e != cudaSuccess) return e;
     configured[dev][variant] = true;
   }
-  kern<<<grid, kSweepWarps * 32, smem, stream>>>(P, src_map, dst_map);
-  return cudaGetLastError();
+  return launch_pdl(kern, grid, kSweepWarps * 32, smem, stream, P, src_map, dst_map);
 }
 
 }  // namespace b2i

@@ -19,6 +19,7 @@
 // Exact: every lane stays below 65536 (normalised non-negative kernels, checked by the planner).
 #include "b200img.h"
 #include "device_utils.cuh"
+#include "launch_pdl.hpp"
 #include "sweep_hooks.cuh"
 #include "sweep5.hpp"
 
@@ -99,6 +100,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
   __shared__ __align__(256) uint8_t lut1[256];
   __shared__ __align__(8) uint64_t bars[kS5Warps * NST];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_launch_dependents();   // the next launch in the stream may set itself up behind this one
   for (int i = threadIdx.x; i < 64; i += kS5Warps * 32)
     reinterpret_cast<uint32_t*>(lut1)[i] = reinterpret_cast<const uint32_t*>(P.lut1)[i];
   if (threadIdx.x == 0) {
@@ -108,6 +110,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
     if (!(MG && P.plain_dst_ptr)) tma_prefetch_desc(&dst_map);
   }
   __syncthreads();  // the only block-wide barrier of the kernel
+  pdl_wait();       // the launch before this one has completed: its output may be this one's input
 
   uint8_t* in_ring = smem + warp * P.warp_smem;          // NST stages of CH rows x kS5InBytes
   uint8_t* out_ring = in_ring + NST * P.in_stage_bytes;  // 2 staging buffers of CH rows x kS5OutBytes
@@ -412,7 +415,6 @@ cudaError_t launch_sweep5(const Sweep5Params& P, const CUtensorMap& src_map, con
     return cudaLaunchCooperativeKernel((const void*)kern, dim3(grid), dim3(kS5Warps * 32), args,
                                        (size_t)P.warp_smem * kS5Warps, stream);
   }
-  kern<<<grid, kS5Warps * 32, P.warp_smem * kS5Warps, stream>>>(P, src_map, dst_map, src_map, dst_map);
-  return cudaGetLastError();
+  return launch_pdl(kern, grid, kS5Warps * 32, (size_t)P.warp_smem * kS5Warps, stream, P, src_map, dst_map, src_map, dst_map);
 }
 }  // namespace b2i

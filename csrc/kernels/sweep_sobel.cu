@@ -15,6 +15,7 @@
 // one below is folded into the state once per strip. The row loop itself carries no border rules.
 #include "b200img.h"
 #include "device_utils.cuh"
+#include "launch_pdl.hpp"
 #include "sweep_hooks.cuh"
 #include "sweep_sobel.hpp"
 
@@ -61,6 +62,7 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
   __shared__ __align__(256) uint8_t lut1[256];
   __shared__ __align__(8) uint64_t bars[kSSWarps * NST];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_launch_dependents();   // the next launch in the stream may set itself up behind this one
   for (int i = threadIdx.x; i < 64; i += kSSWarps * 32)
     reinterpret_cast<uint32_t*>(lut1)[i] = reinterpret_cast<const uint32_t*>(P.lut1)[i];
   if (threadIdx.x == 0) {
@@ -70,6 +72,7 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
     if (!(MG && P.plain_dst_ptr)) tma_prefetch_desc(&dst_map);
   }
   __syncthreads();  // the only block-wide barrier of the kernel
+  pdl_wait();       // the launch before this one has completed: its output may be this one's input
 
   uint8_t* in_ring = smem + warp * P.warp_smem;          // NST stages of CH rows x kSSInBytes
   uint8_t* out_ring = in_ring + NST * P.in_stage_bytes;  // 2 staging buffers of CH rows x kSSOutBytes
@@ -284,7 +287,6 @@ cudaError_t launch_sweep_sobel(const SweepSobelParams& P, const CUtensorMap& src
     if (e != cudaSuccess) return e;
     configured[dev][mg] = true;
   }
-  kern<<<grid, kSSWarps * 32, P.warp_smem * kSSWarps, stream>>>(P, src_map, dst_map);
-  return cudaGetLastError();
+  return launch_pdl(kern, grid, kSSWarps * 32, (size_t)P.warp_smem * kSSWarps, stream, P, src_map, dst_map);
 }
 }  // namespace b2i
