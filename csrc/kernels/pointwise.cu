@@ -213,13 +213,13 @@ cudaError_t launch_pointwise(const PointwiseParams& P, int grid, cudaStream_t st
   const int key = P.cin * 100 + P.gray * 10 + (P.expand ? 1 : 0);
   cudaError_t e = cudaSuccess;
   switch (key) {
-    case 310: e = launch_pdl(pointwise_kernel<3, 1, false>, grid, kPwThreads, 0, stream, P); break;
-    case 311: e = launch_pdl(pointwise_kernel<3, 1, true>, grid, kPwThreads, 0, stream, P); break;
-    case 320: e = launch_pdl(pointwise_kernel<3, 2, false>, grid, kPwThreads, 0, stream, P); break;
-    case 321: e = launch_pdl(pointwise_kernel<3, 2, true>, grid, kPwThreads, 0, stream, P); break;
-    case 300: e = launch_pdl(pointwise_kernel<3, 0, false>, grid, kPwThreads, 0, stream, P); break;
-    case 100: e = launch_pdl(pointwise_kernel<1, 0, false>, grid, kPwThreads, 0, stream, P); break;
-    case 101: e = launch_pdl(pointwise_kernel<1, 0, true>, grid, kPwThreads, 0, stream, P); break;
+    case 310: e = launch_pdl(true, pointwise_kernel<3, 1, false>, grid, kPwThreads, 0, stream, P); break;
+    case 311: e = launch_pdl(true, pointwise_kernel<3, 1, true>, grid, kPwThreads, 0, stream, P); break;
+    case 320: e = launch_pdl(true, pointwise_kernel<3, 2, false>, grid, kPwThreads, 0, stream, P); break;
+    case 321: e = launch_pdl(true, pointwise_kernel<3, 2, true>, grid, kPwThreads, 0, stream, P); break;
+    case 300: e = launch_pdl(true, pointwise_kernel<3, 0, false>, grid, kPwThreads, 0, stream, P); break;
+    case 100: e = launch_pdl(true, pointwise_kernel<1, 0, false>, grid, kPwThreads, 0, stream, P); break;
+    case 101: e = launch_pdl(true, pointwise_kernel<1, 0, true>, grid, kPwThreads, 0, stream, P); break;
     default: return cudaErrorInvalidValue;
   }
   return e;

@@ -563,7 +563,7 @@ cudaError_t launch_stencil_mma(const StencilMmaParams& P, const CUtensorMap& src
     if (e != cudaSuccess) return e;
     configured[dev][variant] = true;
   }
-  return launch_pdl(kern, grid, kSmThreads, smem, stream, P, src_map, dst_map);
+  return launch_pdl(true, kern, grid, kSmThreads, smem, stream, P, src_map, dst_map);
 }
 
 }  // namespace b2i

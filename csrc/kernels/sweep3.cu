@@ -362,7 +362,7 @@ cudaError_t launch_sweep3(const SweepParams& P, const CUtensorMap& src_map, cons
     if (e != cudaSuccess) return e;
     configured[dev][variant] = true;
   }
-  return launch_pdl(kern, grid, kSweepWarps * 32, smem, stream, P, src_map, dst_map);
+  return launch_pdl(true, kern, grid, kSweepWarps * 32, smem, stream, P, src_map, dst_map);
 }
 
 }  // namespace b2i

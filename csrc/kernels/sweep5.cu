@@ -129,7 +129,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
   const int total_warps = gridDim.x * kS5Warps;
   // Fewer tasks than warps (small bands): warp w of CTA c is global warp w * gridDim.x + c, so every SM gets
   // its share of the busy warps instead of some SMs a full CTA and others none. Otherwise CTA by CTA.
-  const int global_warp = P.n_tasks < total_warps ? warp * (int)gridDim.x + (int)blockIdx.x : (int)blockIdx.x * kS5Warps + warp;
+  const int global_warp = !MG && P.n_tasks < total_warps ? warp * (int)gridDim.x + (int)blockIdx.x : (int)blockIdx.x * kS5Warps + warp;
   // Resident multi-pass launches walk the passes here; every other launch is one pass.
   const int n_passes = MG ? max(1, P.n_passes) : 1;
   for (int pass = 0; pass < n_passes; ++pass) {
@@ -415,6 +415,10 @@ cudaError_t launch_sweep5(const Sweep5Params& P, const CUtensorMap& src_map, con
     return cudaLaunchCooperativeKernel((const void*)kern, dim3(grid), dim3(kS5Warps * 32), args,
                                        (size_t)P.warp_smem * kS5Warps, stream);
   }
-  return launch_pdl(kern, grid, kS5Warps * 32, (size_t)P.warp_smem * kS5Warps, stream, P, src_map, dst_map, src_map, dst_map);
+  // Measured on 540-row bands (7680 wide, gauss5): alone on a GPU, dealing the tasks across the CTAs takes a pass
+  // from 14.6 to 12.5 us and the dependent launch to 10.2; with neighbours to push to and wait for, both cost time
+  // (17.4 -> 20.0 us): launches with multi-GPU hooks keep the CTA-by-CTA order, and the plain launch on small bands.
+  return launch_pdl(!mg || P.y1 - P.y0 >= pdl_min_rows_mg(), kern, grid, kS5Warps * 32, (size_t)P.warp_smem * kS5Warps, stream, P, src_map,
+                    dst_map, src_map, dst_map);
 }
 }  // namespace b2i

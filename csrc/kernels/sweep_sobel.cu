@@ -84,7 +84,7 @@ sweep_sobel_kernel(const __grid_constant__ SweepSobelParams P, const __grid_cons
   const int total_warps = gridDim.x * kSSWarps;
   // Fewer tasks than warps (small bands): warp w of CTA c is global warp w * gridDim.x + c, so every SM gets
   // its share of the busy warps instead of some SMs a full CTA and others none. Otherwise CTA by CTA.
-  const int global_warp = P.n_tasks < total_warps ? warp * (int)gridDim.x + (int)blockIdx.x : (int)blockIdx.x * kSSWarps + warp;
+  const int global_warp = !MG && P.n_tasks < total_warps ? warp * (int)gridDim.x + (int)blockIdx.x : (int)blockIdx.x * kSSWarps + warp;
   for (int task = global_warp; task < P.n_tasks; task += total_warps) {
     // boundary segments first: their rows feed the neighbours' next pass
     const int so = task / P.n_strips, strip = task - so * P.n_strips;
@@ -287,6 +287,8 @@ cudaError_t launch_sweep_sobel(const SweepSobelParams& P, const CUtensorMap& src
     if (e != cudaSuccess) return e;
     configured[dev][mg] = true;
   }
-  return launch_pdl(kern, grid, kSSWarps * 32, (size_t)P.warp_smem * kSSWarps, stream, P, src_map, dst_map);
+  // (small bands with multi-GPU hooks: plain launch, see launch_sweep5)
+  return launch_pdl(!mg || P.y1 - P.y0 >= pdl_min_rows_mg(), kern, grid, kSSWarps * 32, (size_t)P.warp_smem * kSSWarps, stream, P, src_map,
+                    dst_map);
 }
 }  // namespace b2i
