@@ -127,9 +127,22 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
 
   uint32_t n_in = 0, n_out = 0;  // boxes consumed / stored by this warp so far
   const int total_warps = gridDim.x * kS5Warps;
-  // Fewer tasks than warps (small bands): warp w of CTA c is global warp w * gridDim.x + c, so every SM gets
-  // its share of the busy warps instead of some SMs a full CTA and others none. Otherwise CTA by CTA.
-  const int global_warp = !MG && P.n_tasks < total_warps ? warp * (int)gridDim.x + (int)blockIdx.x : (int)blockIdx.x * kS5Warps + warp;
+  // Tasks are dealt to warps CTA by CTA. With fewer tasks than warps (small bands) they are dealt across the
+  // CTAs instead, so that every SM gets its share of the busy warps rather than some SMs a full CTA and others
+  // none. With neighbours to push to, the boundary tasks (the first 2 n_strips, short, on every neighbour's
+  // critical path) keep CTAs of their own and only the tasks between them are dealt across the other CTAs.
+  int global_warp = (int)blockIdx.x * kS5Warps + warp;
+  if (P.n_tasks < total_warps) {
+    if (!MG) {
+      global_warp = warp * (int)gridDim.x + (int)blockIdx.x;
+    } else if (P.bseg > 0) {
+      const int nb = 2 * P.n_strips, cb = (nb + kS5Warps - 1) / kS5Warps, rest = (int)gridDim.x - cb;
+      if (rest > 0 && rest * kS5Warps >= P.n_tasks - nb) {
+        if ((int)blockIdx.x < cb) global_warp = global_warp < nb ? global_warp : P.n_tasks;
+        else global_warp = nb + warp * rest + ((int)blockIdx.x - cb);
+      }
+    }
+  }
   // Resident multi-pass launches walk the passes here; every other launch is one pass.
   const int n_passes = MG ? max(1, P.n_passes) : 1;
   for (int pass = 0; pass < n_passes; ++pass) {

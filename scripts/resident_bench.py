@@ -44,10 +44,14 @@ for mode in ("fused", "steps"):
         rt.run_resident(plan, P, fused=fused)
     rt.barrier()
     rr = [_timed(lambda: rt.run_resident(plan, P, fused=fused)) / P * 1e3 for _ in range(7)]
+    import time
+    torch.cuda.synchronize(); rt.barrier()
+    t0 = time.perf_counter(); rt.run_resident(plan, P, fused=fused); host_us = (time.perf_counter() - t0) / P * 1e6
+    torch.cuda.synchronize(); rt.barrier()
     st = rt.status()
-    out[mode] = (statistics.median(rr), min(rr), ran, ok, st)
+    out[mode] = (statistics.median(rr), min(rr), ran, ok, st, host_us)
 if rank == 0:
-    for mode, (med, mn, ran, ok, st) in out.items():
-        print(f"N={world} {a.size} {a.chain} x{P} {mode:5s}: {med:7.1f} us/pass (min {mn:.1f}) fused_ran={ran} status={st} check={ok}",
+    for mode, (med, mn, ran, ok, st, host_us) in out.items():
+        print(f"N={world} {a.size} {a.chain} x{P} {mode:5s}: {med:7.1f} us/pass (min {mn:.1f}) fused_ran={ran} status={st} check={ok} host_enqueue={host_us:.1f} us/pass",
               flush=True)
 rt.close()
