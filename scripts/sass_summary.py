@@ -10,7 +10,7 @@ import subprocess
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "mpi_cuda_imagemanipulation_b200", "lib", "libb200img.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
-EVID = ["UTCIMMA", "LDTM.x32", "STTM.x8", "UTCBAR", "UTCATOMSWS.FIND", "UTMALDG.2D", "UTMASTG.2D", "UTMACCTL.PF", "UTMACMDFLUSH", "SYNCS.ARRIVE.TRANS64", "SYNCS.PHASECHK.TRANS64.TRYWAIT",
+EVID = ["ACQBULK", "PREEXIT", "UTMALDG.2D.MULTICAST", "UCGABAR_ARV", "UTCIMMA", "LDTM.x32", "STTM.x8", "UTCBAR", "UTCATOMSWS.FIND", "UTMALDG.2D", "UTMASTG.2D", "UTMACCTL.PF", "UTMACMDFLUSH", "SYNCS.ARRIVE.TRANS64", "SYNCS.PHASECHK.TRANS64.TRYWAIT",
         "SYNCS.EXCH.64", "IDP.4A.U8.S8", "FFMA.RM", "VIMNMX.U16x2", "FENCE.VIEW.ASYNC.S", "STG.E.STRONG.SYS", "LDG.E.STRONG.SYS",
         "ST.E.STRONG.SYS", "LD.E.STRONG.SYS", "LDG.E.NA.128.CONSTANT", "STG.E.NA.128", "STG.E.64", "ST.E.64", "SHFL.UP", "SHFL.DOWN",
         "I2IP", "PRMT", "IMAD", "LDS.64", "LDS.128", "STS.64", "STS.128", "LDS.U8"]
