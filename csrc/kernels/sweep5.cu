@@ -133,7 +133,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
   // critical path) keep CTAs of their own and only the tasks between them are dealt across the other CTAs.
   int global_warp = (int)blockIdx.x * kS5Warps + warp;
   if (P.n_tasks < total_warps) {
-    if (!MG) {
+    if (!MG) {   // (launches that only wait or signal measured slower dealt across: 12.6 -> 17.5 us on a 540-row band)
       global_warp = warp * (int)gridDim.x + (int)blockIdx.x;
     } else if (P.bseg > 0) {
       const int nb = 2 * P.n_strips, cb = (nb + kS5Warps - 1) / kS5Warps, rest = (int)gridDim.x - cb;
@@ -171,8 +171,11 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
     const int xw_in = (xs * 3 - 32) >> 2, xw_out = (xs * 3) >> 2;
     // A task that reads ghost rows, or writes the neighbour's, first sees the neighbour's flag of
     // the previous pass: its rows have landed here and it has finished reading what we overwrite.
-    const bool sig_up = push_nb && P.signal_up_flag && ya < P.y0 + P.push_rows;
-    const bool sig_dn = push_nb && P.signal_dn_flag && yb > P.y1 - P.push_rows;
+    // (near_*: within push_rows of an end of the launch. Those tasks wait; they also signal if there is a
+    // flag to release. A launch may wait without signalling or the reverse: parallel/dist.py, exchange cycles.)
+    const bool near_up = ya < P.y0 + P.push_rows, near_dn = yb > P.y1 - P.push_rows;
+    const bool sig_up = push_nb && P.signal_up_flag && near_up;
+    const bool sig_dn = push_nb && P.signal_dn_flag && near_dn;
     if (multi && pass > 0) {
       // the tasks around this one (strips s-1..s+1 x segments seg-2..seg+2) have finished the pass
       // before: their rows are what this task reads, and they have read what it overwrites
@@ -195,7 +198,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
         const bool up = lane < 3;
         const int s2 = strip + lane % 3 - 1;
         const uint64_t base = up ? P.wait_up_flag : P.wait_dn_flag;
-        const bool need = up ? (ya - 2 < P.y0 || sig_up) : (yb + 2 > P.y1 || sig_dn);
+        const bool need = up ? (ya - 2 < P.y0 || near_up) : (yb + 2 > P.y1 || near_dn);
         if (base && need && s2 >= 0 && s2 < P.n_strips &&
             !wait_flag_ge(reinterpret_cast<const uint32_t*>(base) + s2, P.wait_epoch + (uint32_t)pass, P.timeout_ns,
                           reinterpret_cast<const uint32_t*>(P.status)))
@@ -205,7 +208,7 @@ sweep5_kernel(const __grid_constant__ Sweep5Params P, const __grid_constant__ CU
       if (lane == 0) asm volatile("fence.proxy.async;" ::: "memory");
     }
     if (lane == 0) {
-      if (wait_nb && !(MG && P.strip_flags)) sweep_wait_neighbours(P, ya, yb, 2, sig_up, sig_dn, (uint32_t)pass);
+      if (wait_nb && !(MG && P.strip_flags)) sweep_wait_neighbours(P, ya, yb, 2, near_up, near_dn, (uint32_t)pass);
       for (int c = 0; c < min(NST, n_chunks); ++c) {
         const uint32_t st = (n_in + c) % NST;
         mbar_arrive_expect_tx(&bar[st], CH * kS5InBytes);
@@ -431,7 +434,8 @@ cudaError_t launch_sweep5(const Sweep5Params& P, const CUtensorMap& src_map, con
   // Measured on 540-row bands (7680 wide, gauss5): alone on a GPU, dealing the tasks across the CTAs takes a pass
   // from 14.6 to 12.5 us and the dependent launch to 10.2; with neighbours to push to and wait for, both cost time
   // (17.4 -> 20.0 us): launches with multi-GPU hooks keep the CTA-by-CTA order, and the plain launch on small bands.
-  return launch_pdl(!mg || P.y1 - P.y0 >= pdl_min_rows_mg(), kern, grid, kS5Warps * 32, (size_t)P.warp_smem * kS5Warps, stream, P, src_map,
+  const bool pushes = P.push_up_ptr || P.push_dn_ptr;
+  return launch_pdl(!pushes || P.y1 - P.y0 >= pdl_min_rows_mg(), kern, grid, kS5Warps * 32, (size_t)P.warp_smem * kS5Warps, stream, P, src_map,
                     dst_map, src_map, dst_map);
 }
 }  // namespace b2i

@@ -244,12 +244,13 @@ int try_sweep5(b2i_plan* plan, const Segment& seg, const b2i_launch_t& L, int y0
   }
   P.n_strips = (L.W + kS5Strip - 1) / kS5Strip;
   const int resident = sms * kS5CtasPerSm * kS5Warps;
-  if (pushes && y1 - y0 >= 4 * kS5Chunk && L.push_rows <= kS5Chunk && !B2I_ENV("B200IMG_NO_BSEG", 0)) {
-    // a launch that pushes halo rows: one-box first and last segments, which run first and are short,
-    // so the rows and the flag are with the neighbour while the other tasks still work
+  if (pushes && y1 - y0 >= 6 * kS5Chunk && L.push_rows <= 2 * kS5Chunk && !B2I_ENV("B200IMG_NO_BSEG", 0)) {
+    // a launch that pushes halo rows: first and last segments of one box (two when more than five rows
+    // leave: exchange cycles), which run first and are short, so the rows and the flag are with the
+    // neighbour while the other tasks still work
     // (every segment but the last is whole boxes: a ragged box would spill into the rows below it)
-    P.bseg = kS5Chunk;
-    const int mid = (y1 - y0 - 2 * kS5Chunk) / kS5Chunk * kS5Chunk;
+    P.bseg = (L.push_rows + kS5Chunk - 1) / kS5Chunk * kS5Chunk;
+    const int mid = (y1 - y0 - 2 * P.bseg) / kS5Chunk * kS5Chunk;
     P.bseg_last = y1 - y0 - P.bseg - mid;
     P.seg_rows = sweep_seg_rows(P.n_strips, mid, std::max(kS5Warps, resident - 2 * P.n_strips), kS5Chunk, 5, 120, 4);
     P.n_segs = 2 + (mid + P.seg_rows - 1) / P.seg_rows;

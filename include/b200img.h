@@ -367,6 +367,11 @@ int b2i_cuda_run_steps(b2i_plan_t* plan, const b2i_launch_t* launch, int steps, 
  * descriptions, halo flags waited/signalled with epochs epoch_base+p / epoch_base+p+1. */
 int b2i_cuda_run_resident_steps(b2i_plan_t* plan, const b2i_launch_t* even, const b2i_launch_t* odd,
                                 int passes, uint32_t epoch_base);
+/* The same with a cycle of `period` launch descriptions, pass p running descs[p % period]: halo rows are
+ * exchanged every few passes only, the passes between compute a shrinking margin of ghost rows themselves
+ * (parallel/dist.py, run_resident(cycle=...)). */
+int b2i_cuda_run_resident_cycle(b2i_plan_t* plan, const b2i_launch_t* descs, int period, int passes,
+                                uint32_t epoch_base);
 /* The same passes in ONE cooperative kernel launch (one separable 3-channel stencil, e.g. gauss5):
  * the kernel walks the passes itself, tasks wait for the tasks around them through `task_flags`
  * (n_task_flags u32 of local device memory, zeroed once when allocated and only ever growing:

@@ -208,6 +208,7 @@ _sig("b2i_cuda_set_flags", C.c_int, _P(C.c_uint64), C.c_int, C.c_uint32, C.c_voi
 _sig("b2i_cuda_run_steps", C.c_int, C.c_void_p, _P(Launch), C.c_int, C.c_uint32, _P(C.c_uint64), C.c_int,
      C.c_uint64)
 _sig("b2i_cuda_run_resident_steps", C.c_int, C.c_void_p, _P(Launch), _P(Launch), C.c_int, C.c_uint32)
+_sig("b2i_cuda_run_resident_cycle", C.c_int, C.c_void_p, _P(Launch), C.c_int, C.c_int, C.c_uint32)
 _sig("b2i_cuda_run_resident_fused", C.c_int, C.c_void_p, _P(Launch), _P(Launch), C.c_int, C.c_uint32, C.c_uint64,
      C.c_int)
 _sig("b2i_cuda_memcpy2d", C.c_int, C.c_uint64, C.c_size_t, C.c_uint64, C.c_size_t, C.c_size_t, C.c_size_t,

@@ -294,7 +294,9 @@ class DistRuntime:
         bp = (W * 3 + 15) // 16 * 16
         rows = max(band_rows(H, self.world, r)[1] - band_rows(H, self.world, r)[0] for r in range(self.world))
         self.rgeom = dict(W=W, H=H, C=Cn, bp=bp)
-        self.band = [self.symmetric(bp * (rows + 2 * G)), self.symmetric(bp * (rows + 2 * G))]
+        # two band buffers ping-pong; run_resident_cycle rotates through four (see there)
+        self.band = [self.symmetric(bp * (rows + 2 * G)) for _ in range(4)]
+        self._last_out = None
         self.y0, self.y1 = band_rows(H, self.world, self.rank)   # resident bands are equal: no root link involved
 
     def scatter_resident(self, src_ptr_on_root: int, src_pitch: int):
@@ -306,36 +308,88 @@ class DistRuntime:
                                     self.stream()))
         self.barrier()
 
-    def _resident_launch(self, inb: int, halo: int, no_tma=False, plan=None, strip_flags=False) -> Launch:
+    def _resident_launch(self, inb: int, halo: int, no_tma=False, plan=None, strip_flags=False,
+                         ext: int = 0, push: bool = True, outb=None, wait: bool = True, signal: bool = True) -> Launch:
+        """One pass over this rank's band: reads band buffer `inb`, writes `outb` (default: the other one
+        of the pair). The rest is for run_resident_cycle:
+        ext > 0: the pass also computes `ext` ghost rows above and below the band (towards neighbours
+        only; the image ends where it ends) from the deeper ghost rows of its input.
+        push=False: no halo rows leave. wait / signal: whether the tasks near the band's ends wait for the
+        neighbours' flags / release the neighbours' flags when they are done."""
         g = self.rgeom
-        outb = inb ^ 1
+        outb = inb ^ 1 if outb is None else outb
         L = Launch()
-        L.W, L.H, L.y0, L.y1 = g["W"], g["H"], self.y0, self.y1
+        up = self.rank - 1 if self.rank > 0 else None
+        dn = self.rank + 1 if self.rank + 1 < self.world else None
+        ya = self.y0 - (ext if up is not None else 0)
+        yb = self.y1 + (ext if dn is not None else 0)
+        L.W, L.H, L.y0, L.y1 = g["W"], g["H"], ya, yb
         self._attach_tmp(L, plan, g["W"], g["H"])
         va, vb = max(0, self.y0 - G), min(g["H"], self.y1 + G)
         L.src = View(self.band[inb].local + g["bp"] * (va - (self.y0 - G)), g["bp"], va, vb)
-        L.dst = View(self.band[outb].local + g["bp"] * G, g["bp"], self.y0, self.y1)
-        up = self.rank - 1 if self.rank > 0 else None
-        dn = self.rank + 1 if self.rank + 1 < self.world else None
+        L.dst = View(self.band[outb].local + g["bp"] * (G - (self.y0 - ya)), g["bp"], ya, yb)
         L.counters = self.words.local + W_COUNTERS
         L.status = self.words.local + W_STATUS
         if halo > 0:
-            L.push_rows = halo
+            # rows from each end of the launch whose tasks wait and signal: with push, the rows that leave;
+            # without, the rows whose stencil reads ghost rows (ext of them are ghost rows themselves)
+            L.push_rows = halo if push else ext + halo
             if up is not None:
                 uy0, uy1 = band_rows(g["H"], self.world, up)
-                L.push_up = View(self.band[outb].ptrs[up] + g["bp"] * (G + (uy1 - uy0)), g["bp"], self.y0, self.y0 + G)
-                L.wait_up_flag = self.words.local + (W_SF_UP if strip_flags else W_FLAG_UP)
-                L.signal_up_flag = self.words.ptrs[up] + (W_SF_DN if strip_flags else W_FLAG_DN)
+                if push:
+                    L.push_up = View(self.band[outb].ptrs[up] + g["bp"] * (G + (uy1 - uy0)), g["bp"], self.y0, self.y0 + G)
+                if wait:
+                    L.wait_up_flag = self.words.local + (W_SF_UP if strip_flags else W_FLAG_UP)
+                if signal:
+                    L.signal_up_flag = self.words.ptrs[up] + (W_SF_DN if strip_flags else W_FLAG_DN)
             if dn is not None:
-                L.push_dn = View(self.band[outb].ptrs[dn] + g["bp"] * (G - halo), g["bp"], self.y1 - halo, self.y1)
-                L.wait_dn_flag = self.words.local + (W_SF_DN if strip_flags else W_FLAG_DN)
-                L.signal_dn_flag = self.words.ptrs[dn] + (W_SF_UP if strip_flags else W_FLAG_UP)
+                if push:
+                    L.push_dn = View(self.band[outb].ptrs[dn] + g["bp"] * (G - halo), g["bp"], self.y1 - halo, self.y1)
+                if wait:
+                    L.wait_dn_flag = self.words.local + (W_SF_DN if strip_flags else W_FLAG_DN)
+                if signal:
+                    L.signal_dn_flag = self.words.ptrs[dn] + (W_SF_UP if strip_flags else W_FLAG_UP)
         L.stream = self.stream()
         L.timeout_ns = self.timeout_ns
         L.flags = (_lib.LAUNCH_NO_TMA if no_tma else 0) | (_lib.LAUNCH_STRIP_FLAGS if strip_flags else 0)
         return L
 
     N_TASK_FLAGS = 16384
+
+    def run_resident_cycle(self, plan, passes: int, cycle: int) -> None:
+        """`passes` applications with halo rows exchanged only every `cycle` passes (2 or 4; `passes` must
+        be a multiple; cycle * halo <= the G = 8 ghost rows). Same result, bit for bit.
+
+        Pass 0 of a cycle reads cycle * halo ghost rows the neighbours pushed and also computes
+        (cycle - 1) * halo of them for itself, the next pass (cycle - 2) * halo, ...; the last pass computes
+        the band only and pushes its first and last cycle * halo rows. Only pass 0 waits (for the rows) and
+        only the last pass signals (that they are there); the passes between are ordinary single-GPU
+        launches. No flag says "I am done reading": the cycles alternate between two PAIRS of band buffers
+        (0, 1) and (2, 3), the last pass of a cycle writing (and pushing) into the other pair. A GPU pushes
+        into a neighbour's buffer after it has seen, in its own pass 0, the neighbour's signal of the
+        cycle before, which the neighbour sent after it had finished every pass that touched the ghost rows
+        of that buffer. One launch per pass (`b2i_cuda_run_resident_cycle`)."""
+        halo = plan.halo
+        if cycle not in (2, 4) or passes % cycle or cycle * halo > G:
+            raise ValueError(f"cycle {cycle} with halo {halo}: need cycle in (2, 4), passes % cycle == 0, cycle * halo <= {G}")
+        if self.y1 > self.y0:
+            descs = (Launch * (2 * cycle))()
+            for c in range(2):
+                pair, other = ((0, 1), 2) if c == 0 else ((2, 3), 0)
+                for j in range(cycle):
+                    last = j == cycle - 1
+                    inb = pair[j & 1]
+                    if last:      # the band only; its ends go to the neighbours' ghost rows of the other pair
+                        L = self._resident_launch(inb, cycle * halo, False, plan, outb=other, wait=False)
+                    elif j == 0:  # reads what the neighbours pushed
+                        L = self._resident_launch(inb, halo, False, plan, ext=(cycle - 1) * halo, push=False,
+                                                  outb=pair[1], signal=False)
+                    else:         # no neighbour involved
+                        L = self._resident_launch(inb, 0, False, plan, ext=(cycle - 1 - j) * halo, outb=pair[(j & 1) ^ 1])
+                    descs[c * cycle + j] = L
+            check(lib.b2i_cuda_run_resident_cycle(plan.handle, descs, 2 * cycle, passes, self.epoch))
+        self._last_out = 2 if (passes // cycle) % 2 == 1 else 0
+        self.epoch += passes + 1
 
     def run_resident(self, plan, passes: int, no_tma: bool = False, fused: bool = True) -> bool:
         """`passes` applications of the plan's chain to the resident bands, halo rows pushed between
@@ -346,6 +400,7 @@ class DistRuntime:
         if halo > G:
             raise ValueError(f"resident passes support a halo of at most {G} rows per pass")
         even, odd = self._resident_launch(0, halo, no_tma, plan), self._resident_launch(1, halo, no_tma, plan)
+        self._last_out = None
         ran_fused = False
         if self.y1 > self.y0:
             if fused and not no_tma:
@@ -366,7 +421,8 @@ class DistRuntime:
     def gather_resident(self, passes: int, dst_ptr_on_root: int, dst_pitch: int, out_c: int):
         g = self.rgeom
         check(lib.b2i_cuda_memcpy2d(dst_ptr_on_root + dst_pitch * self.y0, dst_pitch,
-                                    self.band[passes & 1].local + g["bp"] * G, g["bp"], g["W"] * out_c,
+                                    self.band[passes & 1 if self._last_out is None else self._last_out].local + g["bp"] * G,
+                                    g["bp"], g["W"] * out_c,
                                     self.y1 - self.y0, 2, self.stream()))
         self.barrier()
 
@@ -447,6 +503,26 @@ def _resident_extra(rt, chain: str, W: int, H: int, img, checked: dict, key: str
             rt.barrier()
             rr = [_timed(lambda: rt.run_resident(plan, p_time, fused=mode == "fused")) / p_time for _ in range(5)]
             out[mode + "_ms_per_pass"] = round(statistics.median(rr), 5)
+        # halo rows exchanged every 2 / 4 passes only, the ghost rows between computed locally (run_resident_cycle):
+        # checked like the others, then timed
+        for cyc in (2, 4):
+            if cyc * plan.halo > G or p_check % cyc or p_time % cyc or "," in chain:
+                continue
+            rt.scatter_resident(rt.src.ptrs[0], rt.geom["sp"])
+            rt.run_resident_cycle(plan, p_check, cyc)
+            rt.barrier()
+            rt.gather_resident(p_check, rt.dst.ptrs[0], rt.geom["dp"], 3)
+            got = rt.fetch_root()
+            if rank == 0:
+                c = _check_rows(",".join([chain] * p_check), img, got, _boundary_rows(H, bands))
+                checked[key][f"exchange_every_{cyc}_ok"] = c["ok"]
+                checked[key]["ok"] = ok = ok and c["ok"]
+            del got
+            rt.scatter_resident(rt.src.ptrs[0], rt.geom["sp"])
+            rt.run_resident_cycle(plan, p_time, cyc)
+            rt.barrier()
+            rr = [_timed(lambda: rt.run_resident_cycle(plan, p_time, cyc)) / p_time for _ in range(5)]
+            out[f"exchange_every_{cyc}_ms_per_pass"] = round(statistics.median(rr), 5)
         best = min(v for k, v in out.items() if k.endswith("_ms_per_pass"))
         out.update(ms_per_pass=best, mpix_per_s=round(W * H / 1e6 / (best / 1e3), 1), status=rt.status(), checked_ok=ok)
         if rank == 0 and not ok:

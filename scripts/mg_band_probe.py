@@ -42,6 +42,8 @@ for size in sys.argv[1:] or ["7680x540", "7680x1080", "7680x2160"]:
                     L.wait_up_flag, L.wait_dn_flag = words.data_ptr() + 32, words.data_ptr() + 36
                 if not os.environ.get("PROBE_NO_SIGNAL"):
                     L.signal_up_flag, L.signal_dn_flag = words.data_ptr() + 128, words.data_ptr() + 132
+                if os.environ.get("PROBE_NO_PUSH"):
+                    L.push_rows = 0; L.push_up = View(0, 0, 0, 0); L.push_dn = View(0, 0, 0, 0)
                 if os.environ.get("PROBE_ONE_SIDE"):
                     L.push_dn = View(0, 0, 0, 0); L.wait_dn_flag = 0; L.signal_dn_flag = 0
             ls.append(L)

@@ -16,6 +16,7 @@ ap.add_argument("--size", default="7680x4320")
 ap.add_argument("--chain", default="gauss5")
 ap.add_argument("--passes", type=int, default=8)
 ap.add_argument("--check", type=int, default=1)
+ap.add_argument("--cycle", type=int, default=0, help="also time halo exchanges every CYCLE passes (2 or 4)")
 a = ap.parse_args()
 W, H = (int(x) for x in a.size.split("x"))
 rt = DistRuntime(root=0)
@@ -27,10 +28,17 @@ rt.load_root(img)
 rt.setup_resident(W, H, 3)
 P = a.passes
 out = {}
-for mode in ("fused", "steps"):
+def run(mode):
+    if mode == "cycle":
+        rt.run_resident_cycle(plan, P, a.cycle)
+        return False
+    return rt.run_resident(plan, P, fused=mode == "fused")
+
+
+for mode in ("fused", "steps") + (("cycle",) if a.cycle else ()):
     fused = mode == "fused"
     rt.scatter_resident(rt.src.ptrs[0], rt.geom["sp"])
-    ran = rt.run_resident(plan, P, fused=fused)
+    ran = run(mode)
     rt.barrier()
     ok = None
     if a.check:
@@ -41,12 +49,12 @@ for mode in ("fused", "steps"):
             ok = _check_rows(",".join([a.chain] * P), img, got, _boundary_rows(H, bands))
     rt.scatter_resident(rt.src.ptrs[0], rt.geom["sp"])
     for _ in range(2):
-        rt.run_resident(plan, P, fused=fused)
+        run(mode)
     rt.barrier()
-    rr = [_timed(lambda: rt.run_resident(plan, P, fused=fused)) / P * 1e3 for _ in range(7)]
+    rr = [_timed(lambda: run(mode)) / P * 1e3 for _ in range(7)]
     import time
     torch.cuda.synchronize(); rt.barrier()
-    t0 = time.perf_counter(); rt.run_resident(plan, P, fused=fused); host_us = (time.perf_counter() - t0) / P * 1e6
+    t0 = time.perf_counter(); run(mode); host_us = (time.perf_counter() - t0) / P * 1e6
     torch.cuda.synchronize(); rt.barrier()
     st = rt.status()
     out[mode] = (statistics.median(rr), min(rr), ran, ok, st, host_us)
