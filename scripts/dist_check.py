@@ -51,6 +51,26 @@ def main():
             ok = np.array_equal(got, want) and st == 0
             fails += not ok
             print(f"resid {chain:28s} {W}x{H} passes={passes}: {'OK' if ok else 'MISMATCH'} status={st}", flush=True)
+    # halo rows exchanged every `cycle` passes only (run_resident_cycle): the whole image, bit for bit
+    for chain, W, H, passes, cycle in [("gauss5", 1024, 330, 4, 2), ("gauss5", 1024, 330, 8, 4), ("gauss3", 2048, 500, 8, 4),
+                                       ("gauss5", 7680, 1080, 4, 4), ("gauss5@replicate", 2048, 64 * world + 3, 6, 2)]:
+        img = b2.synth_image(W, H, 3, seed=passes + cycle)
+        plan = Plan(chain, 3)
+        rt.setup_root(W, H, 3, 3)
+        rt.load_root(img if rank == 0 else None)
+        rt.setup_resident(W, H, 3)
+        rt.scatter_resident(rt.src.ptrs[0], rt.geom["sp"])
+        rt.run_resident_cycle(plan, passes, cycle)
+        rt.gather_resident(passes, rt.dst.ptrs[0], rt.geom["dp"], 3)
+        got = rt.fetch_root()
+        st = rt.status()
+        if rank == 0:
+            want = img
+            for _ in range(passes):
+                want = b2.host_run(chain, want)
+            ok = np.array_equal(got, want) and st == 0
+            fails += not ok
+            print(f"cycle {chain:28s} {W}x{H} passes={passes} exchange every {cycle}: {'OK' if ok else 'MISMATCH'} status={st}", flush=True)
     rt.close()
     if rank == 0:
         print("DIST_CHECK", "PASS" if fails == 0 else f"FAIL({fails})", flush=True)
