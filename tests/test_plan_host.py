@@ -99,3 +99,17 @@ def test_library_path_override():
                        capture_output=True, text=True, env=env,
                        cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     assert r.returncode == 0 and r.stdout.strip() == _lib.LIB_PATH, r.stderr
+
+
+def test_resident_entry_points_reject_bad_arguments_without_a_gpu():
+    """The multi-pass drivers validate before they launch (csrc/runtime/ipc.cu): no plan, no launch
+    descriptions, a cycle period of 0. The reference's only argument check is the image load (kernel.cu:111)."""
+    import ctypes as C
+    from mpi_cuda_imagemanipulation_b200._lib import Launch, lib
+    L = (Launch * 2)()
+    assert lib.b2i_cuda_run_resident_cycle(None, L, 2, 4, 0) != 0
+    plan = Plan("gauss5", 3)
+    assert lib.b2i_cuda_run_resident_cycle(plan.handle, None, 2, 4, 0) != 0
+    assert lib.b2i_cuda_run_resident_cycle(plan.handle, L, 0, 4, 0) != 0
+    assert lib.b2i_cuda_run_resident_cycle(plan.handle, L, 2, 0, 0) == 0      # no passes: nothing to do
+    assert lib.b2i_cuda_run_resident_steps(None, C.byref(L[0]), C.byref(L[1]), 1, 0) != 0
