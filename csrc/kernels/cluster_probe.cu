@@ -125,10 +125,13 @@ extern "C" int b2i_cuda_cluster_probe(int W3, int H, int T, int R, int iters, fl
   B2I_CHECK_ARG(W3 >= kCpWidth && W3 % 16 == 0 && H >= 8 && T >= 8 && T % 8 == 0 && T <= 128 && R >= 1 && R <= 4 && iters >= 1,
                 "bad probe shape W3=%d H=%d T=%d R=%d iters=%d", W3, H, T, R, iters);
   uint8_t *src = nullptr, *dst = nullptr;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
   const size_t bytes = (size_t)W3 * H;
   auto cleanup = [&]() {
     if (src) cudaFree(src);
     if (dst) cudaFree(dst);
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
   };
 #define CP_CUDA(x)                                                                               \
   do {                                                                                           \
@@ -159,7 +162,6 @@ extern "C" int b2i_cuda_cluster_probe(int W3, int H, int T, int R, int iters, fl
   const int smem_bytes = (T + 2 * R) * kCpWidth;
   CP_CUDA(cudaFuncSetAttribute(cluster_probe_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   CP_CUDA(cudaFuncSetAttribute(cluster_probe_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-  cudaEvent_t e0, e1;
   CP_CUDA(cudaEventCreate(&e0));
   CP_CUDA(cudaEventCreate(&e1));
   *mismatches = 0;
@@ -196,8 +198,6 @@ extern "C" int b2i_cuda_cluster_probe(int W3, int H, int T, int R, int iters, fl
         if (out[(size_t)y * W3 + x] != (uint8_t)(a ^ b)) ++*mismatches;
       }
   }
-  cudaEventDestroy(e0);
-  cudaEventDestroy(e1);
   cleanup();
 #undef CP_CUDA
   return B2I_OK;
